@@ -1,0 +1,142 @@
+/* vf_cuda.h -- C ABI of libvfcuda.so: the B200 (sm_100a) replacement for the GPU half of
+ * vulkan-forge's headless render path (what src/shaders/*.wgsl + wgpu do in the reference).
+ *
+ * This is the drop-in boundary.  A Rust host would bind it with `extern "C"` exactly as listed
+ * (see INTEGRATION.md for the Rust/ctypes stubs); in this repository the host above it is the
+ * C++/pybind11 module `_vulkan_forge` because no Rust toolchain exists on the build machines.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a non-zero VF_E_* code otherwise; the message is
+ *     available from vf_last_error() (thread-local, valid until the next call on that thread);
+ *   - no exception or panic crosses the boundary;
+ *   - the caller owns and sizes every host buffer; inputs are borrowed for the call only;
+ *   - handles are not thread-safe; every function synchronises before returning unless its
+ *     name ends in _async;
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry point fails
+ *     with VF_E_NO_DEVICE.
+ * Paths in "replaces:" comments are relative to the reference repository root.
+ */
+#ifndef VF_CUDA_H
+#define VF_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VF_OK 0
+#define VF_E_NO_DEVICE 1   /* no CUDA device / driver ("No suitable GPU adapter") */
+#define VF_E_CUDA 2        /* a CUDA runtime call or kernel failed */
+#define VF_E_INVALID 3     /* invalid argument */
+#define VF_E_OOM 4         /* device or pinned-host allocation failed */
+#define VF_E_IO 5          /* file output failed */
+
+#define VF_MODE_SHIPPED 0   /* bit-faithful restatement of src/shaders/terrain.wgsl */
+#define VF_MODE_NORTHSTAR 1 /* DEM forward-difference normals, [h_min,h_max] LUT, Reinhard */
+
+#define VF_LUT_VIRIDIS 0    /* order of src/colormap/mod.rs:7 SUPPORTED */
+#define VF_LUT_MAGMA 1
+#define VF_LUT_TERRAIN 2
+
+typedef struct vf_scene vf_scene;   /* one terrain renderer: target + DEM + LUT + uniforms */
+typedef struct vf_height vf_height; /* a device-resident R32F height image */
+
+typedef struct {
+    char name[256];
+    int cc_major, cc_minor, sm_count;
+    uint64_t total_mem_bytes;
+    int pci_device_id, pci_bus_id, l2_bytes, max_smem_per_block;
+} vf_device_info_t;
+
+/* per-frame statistics of the last vf_scene_render_* call (last frame of a batch) */
+typedef struct {
+    uint32_t bin_pairs;      /* (tile, primitive) pairs produced by the binning kernel */
+    uint32_t bin_capacity;   /* capacity of the pair buffer (grown automatically) */
+    uint32_t clipped_prims;  /* primitives that took the Sutherland-Hodgman path */
+    uint32_t tiles;          /* screen tiles (16x16 px) */
+    float ms_geom, ms_bin, ms_raster, ms_total; /* CUDA-event times, only when timing enabled */
+} vf_frame_stats_t;
+
+/* ---- context ----------------------------------------------------------------------
+ * replaces: WgpuContext::get() src/lib.rs:31-60 and the per-object device creation in
+ * src/terrain/mod.rs:277-294, src/scene/mod.rs:63-70 */
+int vf_init(int device);                       /* device < 0 : keep current / LOCAL_RANK */
+const char *vf_last_error(void);
+int vf_device_count(int *count);
+int vf_device_info(int device, vf_device_info_t *out);   /* src/lib.rs:744-845 diagnostics */
+/* pinned host memory for zero-staging readback (numpy arrays are built on top of it) */
+int vf_host_alloc(size_t bytes, void **out);
+int vf_host_free(void *p);
+
+/* ---- triangle path ------------------------------------------------------------------
+ * replaces: render_into_offscreen + copy_texture_to_rgba_unpadded, src/lib.rs:162-216,685-721,
+ * and src/shaders/triangle.wgsl.  out: tight uint8[h][w][4]. */
+int vf_triangle_render(int w, int h, uint8_t *out_rgba_host);
+
+/* ---- public grid generator ------------------------------------------------------------
+ * replaces: make_grid + grid_generate, src/terrain/mesh.rs:35-90,149-203.
+ * xy, uv: float[nx*nz*2]; idx: uint32[6*(nx-1)*(nz-1)] (host buffers). */
+int vf_grid_generate(uint32_t nx, uint32_t nz, float dx, float dy,
+                     float *xy, float *uv, uint32_t *idx);
+
+/* ---- DEM statistics -------------------------------------------------------------------
+ * replaces: terrain_stats::min_max src/terrain_stats.rs:11-35 (clamp=1: exact 1/99 percentile of
+ * the strided sample via device radix select), dem_stats_from_slice / normalize_in_place
+ * src/lib.rs:905-951.  `data` is a HOST pointer of n floats. */
+int vf_dem_minmax(const float *data, size_t n, int clamp, float *lo, float *hi);
+int vf_dem_stats(const float *data, size_t n, float out4[4]);        /* min,max,mean,std */
+/* mode 0 = minmax to [lo,hi], 1 = zscore; in place on the host array */
+int vf_dem_normalize(float *data, size_t n, int mode, float eps, float lo, float hi);
+/* f64 -> f32 cast and scale by exaggeration on the device (add_terrain, src/lib.rs:351-388) */
+int vf_dem_ingest_f64(const double *src, size_t n, float scale, float *dst);
+int vf_dem_ingest_f32(const float *src, size_t n, float scale, float *dst);
+
+/* ---- R32F height image round trip -----------------------------------------------------
+ * replaces: Renderer.upload_height_r32f / debug_read_height_patch / read_full_height_texture,
+ * src/lib.rs:496-681 (256-byte row padding is an artefact of wgpu and is gone). */
+int vf_height_upload(const float *host, uint32_t w, uint32_t h, vf_height **out);
+int vf_height_size(const vf_height *t, uint32_t *w, uint32_t *h);
+int vf_height_read_patch(const vf_height *t, uint32_t x, uint32_t y, uint32_t w, uint32_t h,
+                         float *out_host);
+void vf_height_destroy(vf_height *t);
+
+/* ---- colormap -------------------------------------------------------------------------
+ * replaces: colormap::decode_png_rgba8, src/colormap/mod.rs:50-56 (palette bytes embedded) */
+int vf_colormap_rgba8(int lut_id, uint8_t out1024[1024]);
+
+/* ---- terrain scene --------------------------------------------------------------------
+ * replaces: Scene / TerrainSpike GPU state and draw, src/scene/mod.rs:60-335,
+ * src/terrain/mod.rs:258-493, src/terrain/pipeline.rs:19-143, src/shaders/terrain.wgsl.
+ * The render-path grid (src/terrain/mod.rs:553-598) is implicit: no vertex/index buffers. */
+int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_unorm, vf_scene **out);
+void vf_scene_destroy(vf_scene *s);
+/* src/scene/mod.rs:227-276: copies the host array into a device image (pitch multiple of 16 B) */
+int vf_scene_set_height_f32(vf_scene *s, const float *host, uint32_t w, uint32_t h);
+/* TerrainUniforms as 44 f32, src/terrain/mod.rs:114-142 (view, proj column-major, ...) */
+int vf_scene_set_uniforms(vf_scene *s, const float u44[44]);
+int vf_scene_get_uniforms(const vf_scene *s, float u44[44]);
+int vf_scene_set_mode(vf_scene *s, int mode, int depth, float h_min, float h_max);
+/* 1-99 % range of the scene's DEM on the device (+1e-5 guard, src/renderer.rs:24-28) */
+int vf_scene_auto_height_range(vf_scene *s, float *h_min, float *h_max);
+/* render one frame with the stored uniforms; out: tight uint8[h][w][4], row 0 = top */
+int vf_scene_render_rgba(vf_scene *s, uint8_t *out_rgba_host);
+/* n frames, one uniform block each, frames gathered to host (pinned memory recommended) */
+int vf_scene_render_batch(vf_scene *s, const float *u44xn, int n, uint8_t *out_rgba_host);
+/* n frames left in device memory (no D2H); for kernel-only timing */
+int vf_scene_render_device(vf_scene *s, const float *u44xn, int n);
+/* visibility of the last frame: per pixel 0 = clear colour, else primitive id + 1 */
+int vf_scene_debug_visibility(vf_scene *s, uint32_t *out_host);
+int vf_scene_enable_timing(vf_scene *s, int enabled);
+int vf_scene_last_stats(const vf_scene *s, vf_frame_stats_t *out);
+/* run on a caller-owned cudaStream_t (e.g. torch's current stream); NULL = private stream */
+int vf_scene_set_stream(vf_scene *s, void *cuda_stream);
+
+/* ---- PNG ------------------------------------------------------------------------------
+ * replaces: image::RgbaImage::save, src/scene/mod.rs:331-333 (RGBA8, zlib deflate) */
+int vf_png_write(const char *path, const uint8_t *rgba, int w, int h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

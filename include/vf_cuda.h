@@ -1,5 +1,5 @@
 /* vf_cuda.h -- C ABI of libvfcuda.so: the B200 (sm_100a) replacement for the GPU half of
- * vulkan-forge's headless render path (what src/shaders/*.wgsl + wgpu do in the reference).
+ * vulkan-forge's headless render path (what the WGSL shaders under src/shaders plus wgpu do in the reference).
  *
  * This is the drop-in boundary.  A Rust host would bind it with `extern "C"` exactly as listed
  * (see INTEGRATION.md for the Rust/ctypes stubs); in this repository the host above it is the

@@ -1,0 +1,185 @@
+// vf_misc.cu -- triangle path, public grid generator, R32F height image round trip.
+#include <string.h>
+
+#include "vf_device.cuh"
+#include "vf_internal.h"
+
+// ---------------------------------------------------------------------------------------
+// k_triangle: the fixed triangle of src/lib.rs:72-91 through the same snap / edge-function /
+// top-left / sRGB code as the terrain path; src/shaders/triangle.wgsl:1-23 (pass-through
+// position, colour varying), clear WHITE (src/lib.rs:19,703).  One thread = 4 pixels of a row,
+// one 16-byte store.
+__global__ void __launch_bounds__(256)
+k_triangle(uint32_t W, uint32_t H, const float* __restrict__ thr_g, uint8_t* __restrict__ out) {
+    __shared__ float s_thr[256];
+    s_thr[threadIdx.x] = thr_g[threadIdx.x];
+    __syncthreads();
+    const float pos[3][2] = {{-0.8f, -0.8f}, {0.8f, -0.8f}, {0.0f, 0.8f}};
+    const float col[3][3] = {{1.0f, 0.2f, 0.2f}, {0.2f, 1.0f, 0.2f}, {0.2f, 0.2f, 1.0f}};
+    VfFrame f;
+    f.hw = __fmul_rn(0.5f, (float)W); f.hh = __fmul_rn(0.5f, (float)H);
+    VfSubTri t;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        VfVtx v;
+        v.c[0] = pos[k][0]; v.c[1] = pos[k][1]; v.c[2] = 0.0f; v.c[3] = 1.0f;
+#pragma unroll
+        for (int a = 0; a < 5; ++a) v.a[a] = 0.0f;
+        vf_to_screen(f, v, t.v[k]);
+    }
+    const bool front = vf_area2(t) < 0;
+    const uint32_t groups_per_row = (W + 3u) / 4u;
+    const size_t total = (size_t)groups_per_row * H;
+    for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total;
+         g += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t py = (uint32_t)(g / groups_per_row);
+        const uint32_t px0 = (uint32_t)(g - (size_t)py * groups_per_row) * 4u;
+        uint32_t px4[4];
+#pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) {
+            const uint32_t px = px0 + q;
+            uint32_t rgba = 0xffffffffu;
+            int64_t e[3];
+            if (front && px < W && vf_covers(t, (int)px, (int)py, e)) {
+                float b[3];
+                vf_barycentric(e, b);
+                rgba = 0xff000000u;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float c = fmaf(b[2], col[2][k], fmaf(b[1], col[1][k], __fmul_rn(b[0], col[0][k])));
+                    rgba |= vf_srgb_encode(s_thr, c) << (8 * k);
+                }
+            }
+            px4[q] = rgba;
+        }
+        uint8_t* dst = out + ((size_t)py * W + px0) * 4;
+        if ((W & 3u) == 0u) {
+            *reinterpret_cast<uint4*>(dst) = make_uint4(px4[0], px4[1], px4[2], px4[3]);
+        } else {
+            for (uint32_t q = 0; q < 4 && px0 + q < W; ++q) reinterpret_cast<uint32_t*>(dst)[q] = px4[q];
+        }
+    }
+}
+
+struct DevPtr {
+    void* p = nullptr;
+    ~DevPtr() { if (p) cudaFree(p); }
+};
+
+extern "C" int vf_triangle_render(int w, int h, uint8_t* out_rgba_host) {
+    if (w <= 0 || h <= 0 || !out_rgba_host) return vf_set_error(VF_E_INVALID, "invalid size / null output");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    DevPtr d;
+    const size_t bytes = (size_t)w * h * 4;
+    VF_CUDA(cudaMalloc(&d.p, bytes));
+    const size_t groups = (size_t)((w + 3) / 4) * h;
+    const int blocks = (int)((groups + 255) / 256 > 148 * 8 ? 148 * 8 : (groups + 255) / 256);
+    k_triangle<<<blocks, 256>>>((uint32_t)w, (uint32_t)h, vf_srgb_thresholds_dev(), (uint8_t*)d.p);
+    VF_CUDA(cudaGetLastError());
+    VF_CUDA(cudaMemcpy(out_rgba_host, d.p, bytes, cudaMemcpyDeviceToHost));
+    return VF_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// k_grid: src/terrain/mesh.rs:35-90.  Thread = one vertex; the thread of cell (x,y) also writes
+// that cell's 6 indices.  Rust never contracts, so every mul/add/div is a separate rounding.
+__global__ void __launch_bounds__(256)
+k_grid(uint32_t w, uint32_t h, float dx, float dy, float2* __restrict__ xy, float2* __restrict__ uv,
+       uint32_t* __restrict__ idx) {
+    const float wm1 = __fsub_rn((float)w, 1.0f), hm1 = __fsub_rn((float)h, 1.0f);
+    const float cx = __fmul_rn(__fmul_rn(wm1, 0.5f), dx);
+    const float cy = __fmul_rn(__fmul_rn(hm1, 0.5f), dy);
+    const size_t n = (size_t)w * h;
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n;
+         k += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t y = (uint32_t)(k / w), x = (uint32_t)(k - (size_t)y * w);
+        xy[k] = make_float2(__fsub_rn(__fmul_rn((float)x, dx), cx), __fsub_rn(__fmul_rn((float)y, dy), cy));
+        uv[k] = make_float2(__fdiv_rn((float)x, wm1), __fdiv_rn((float)y, hm1));
+        if (x + 1 < w && y + 1 < h) {
+            const uint32_t i0 = y * w + x, i1 = i0 + 1, i2 = i0 + w, i3 = i2 + 1;
+            uint32_t* o = idx + ((size_t)y * (w - 1) + x) * 6;
+            // 24 bytes per cell, 8-byte aligned: three 8-byte stores
+            reinterpret_cast<uint2*>(o)[0] = make_uint2(i0, i1);
+            reinterpret_cast<uint2*>(o)[1] = make_uint2(i2, i2);
+            reinterpret_cast<uint2*>(o)[2] = make_uint2(i1, i3);
+        }
+    }
+}
+
+extern "C" int vf_grid_generate(uint32_t nx, uint32_t nz, float dx, float dy, float* xy, float* uv, uint32_t* idx) {
+    if (nx < 2 || nz < 2) return vf_set_error(VF_E_INVALID, "nx and nz must be >= 2");
+    if (!isfinite(dx) || !isfinite(dy) || dx <= 0.0f || dy <= 0.0f)
+        return vf_set_error(VF_E_INVALID, "spacing components must be finite and > 0");
+    if ((uint64_t)nx * nz > 0xffffffffull) return vf_set_error(VF_E_INVALID, "nx*nz exceeds u32 indices");
+    if (!xy || !uv || !idx) return vf_set_error(VF_E_INVALID, "null output");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    const size_t n = (size_t)nx * nz, m = (size_t)(nx - 1) * (nz - 1) * 6;
+    DevPtr dxy, duv, didx;
+    VF_CUDA(cudaMalloc(&dxy.p, n * 8));
+    VF_CUDA(cudaMalloc(&duv.p, n * 8));
+    VF_CUDA(cudaMalloc(&didx.p, m * 4));
+    const size_t b = (n + 255) / 256;
+    k_grid<<<(int)(b > 148 * 16 ? 148 * 16 : b), 256>>>(nx, nz, dx, dy, (float2*)dxy.p, (float2*)duv.p, (uint32_t*)didx.p);
+    VF_CUDA(cudaGetLastError());
+    VF_CUDA(cudaMemcpy(xy, dxy.p, n * 8, cudaMemcpyDeviceToHost));
+    VF_CUDA(cudaMemcpy(uv, duv.p, n * 8, cudaMemcpyDeviceToHost));
+    VF_CUDA(cudaMemcpy(idx, didx.p, m * 4, cudaMemcpyDeviceToHost));
+    return VF_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// R32F height image: src/lib.rs:496-681.  wgpu's 256-byte row padding has no equivalent here:
+// the image is a pitched device allocation and patches come back with cudaMemcpy2D.
+struct vf_height {
+    float* d = nullptr;
+    uint32_t w = 0, h = 0;
+    size_t pitch = 0;      // bytes
+};
+
+extern "C" int vf_height_upload(const float* host, uint32_t w, uint32_t h, vf_height** out) {
+    if (!host || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "terrain dimensions are zero");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    vf_height* t = new vf_height();
+    t->w = w; t->h = h;
+    t->pitch = (((size_t)w * 4) + 15) & ~(size_t)15;
+    cudaError_t e = cudaMalloc(&t->d, t->pitch * h);
+    if (e == cudaSuccess)
+        e = cudaMemcpy2D(t->d, t->pitch, host, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(t->d);
+        delete t;
+        (void)cudaGetLastError();
+        return vf_set_error(e == cudaErrorMemoryAllocation ? VF_E_OOM : VF_E_CUDA, "height upload: %s", cudaGetErrorString(e));
+    }
+    *out = t;
+    return VF_OK;
+}
+
+extern "C" int vf_height_size(const vf_height* t, uint32_t* w, uint32_t* h) {
+    if (!t) return vf_set_error(VF_E_INVALID, "null height image");
+    if (w) *w = t->w;
+    if (h) *h = t->h;
+    return VF_OK;
+}
+
+extern "C" int vf_height_read_patch(const vf_height* t, uint32_t x, uint32_t y, uint32_t w, uint32_t h, float* out_host) {
+    if (!t || !out_host) return vf_set_error(VF_E_INVALID, "null argument");
+    if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "patch dimensions must be > 0");
+    if ((uint64_t)x + w > t->w)
+        return vf_set_error(VF_E_INVALID, "requested patch exceeds texture bounds in x: x+w (%u) > width (%u)", x + w, t->w);
+    if ((uint64_t)y + h > t->h)
+        return vf_set_error(VF_E_INVALID, "requested patch exceeds texture bounds in y: y+h (%u) > height (%u)", y + h, t->h);
+    const char* src = (const char*)t->d + (size_t)y * t->pitch + (size_t)x * 4;
+    VF_CUDA(cudaMemcpy2D(out_host, (size_t)w * 4, src, t->pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost));
+    return VF_OK;
+}
+
+extern "C" void vf_height_destroy(vf_height* t) {
+    if (!t) return;
+    cudaFree(t->d);
+    delete t;
+}

@@ -1,0 +1,380 @@
+// vf_terrain.cu -- vf_scene: host side of the terrain frame (C ABI in include/vf_cuda.h).
+// replaces: Scene / TerrainSpike GPU state + draw + readback, src/scene/mod.rs:60-335,
+// src/terrain/mod.rs:258-493, src/terrain/pipeline.rs:19-143.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "vf_internal.h"
+#include "vf_terrain_kernels.cuh"
+
+struct vf_scene {
+    int W = 0, H = 0;
+    uint32_t G = 0;
+    int lut_id = 0, lut_unorm = 0;
+    float u44[44];
+    int mode = VF_MODE_SHIPPED, depth = 0;
+    float h_min = -0.5f, h_max = 0.5f;
+    // device state
+    float* d_dem = nullptr; uint32_t Wd = 0, Hd = 0, pitch = 0;   // pitch in floats (mult. of 4)
+    VfAxis* d_axis = nullptr;
+    float4* d_lut = nullptr;
+    uint8_t* d_frame = nullptr;          // n_slots frames of W*H*4 bytes
+    int n_slots = 0;
+    uint32_t* d_vis = nullptr;           // debug visibility (allocated on demand)
+    uint32_t tiles_x = 0, tiles_y = 0, n_tiles = 0;
+    uint32_t* d_tile_count = nullptr;    // [n_tiles] counts | [VF_CNT_WORDS] counters (one memset)
+    uint32_t* d_counters = nullptr;      // = d_tile_count + n_tiles
+    uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [1] high-water mark of pairs
+    uint32_t* d_maxpairs = nullptr;      // = d_tile_off + n_tiles + 1
+    uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
+    uint32_t* d_pair_tile = nullptr; uint32_t* d_pair_prim = nullptr; uint32_t* d_sorted = nullptr;
+    uint32_t capacity = 0;
+    uint32_t* h_counters = nullptr;      // pinned, VF_CNT_WORDS per slot (max 64 slots)
+    cudaStream_t stream = nullptr; bool own_stream = false;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+    bool timing = false;
+    vf_frame_stats_t stats;
+};
+
+static const int VF_MAX_SLOTS = 2;
+
+static void scene_free(vf_scene* s) {
+    if (!s) return;
+    cudaFree(s->d_dem); cudaFree(s->d_axis); cudaFree(s->d_lut); cudaFree(s->d_frame);
+    cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
+    cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
+    cudaFree(s->d_sorted);
+    if (s->h_counters) cudaFreeHost(s->h_counters);
+    for (auto& e : s->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
+    for (auto& e : s->ev_copied) if (e) cudaEventDestroy(e);
+    if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    (void)cudaGetLastError();
+    delete s;
+}
+
+static int scene_alloc_pairs(vf_scene* s, uint32_t capacity) {
+    cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim); cudaFree(s->d_sorted);
+    s->d_pair_tile = s->d_pair_prim = s->d_sorted = nullptr;
+    VF_CUDA(cudaMalloc(&s->d_pair_tile, (size_t)capacity * 4));
+    VF_CUDA(cudaMalloc(&s->d_pair_prim, (size_t)capacity * 4));
+    VF_CUDA(cudaMalloc(&s->d_sorted, (size_t)capacity * 4));
+    s->capacity = capacity;
+    return VF_OK;
+}
+
+// LUT as the fragment stage sees it: linear float per texel.  Rgba8UnormSrgb: exact sRGB EOTF
+// of k/255 (what the sampler does); Rgba8Unorm: the lossy CPU table of
+// src/colormap/mod.rs:59-79 divided by 255.
+static void build_lut(const uint8_t* pal, int unorm, float4* out) {
+    for (int i = 0; i < 256; ++i) {
+        float c[3];
+        for (int k = 0; k < 3; ++k) {
+            const uint8_t v = pal[4 * i + k];
+            if (unorm) {
+                const float sr = (float)v / 255.0f;
+                float lin = sr <= 0.04045f ? sr / 12.92f : powf((sr + 0.055f) / 1.055f, 2.4f);
+                lin = std::min(std::max(lin, 0.0f), 1.0f);
+                const uint8_t q = (uint8_t)(lin * 255.0f + 0.5f);
+                c[k] = (float)q / 255.0f;
+            } else {
+                const double sd = (double)v / 255.0;
+                c[k] = (float)(sd <= 0.04045 ? sd / 12.92 : pow((sd + 0.055) / 1.055, 2.4));
+            }
+        }
+        out[i] = make_float4(c[0], c[1], c[2], 1.0f);
+    }
+}
+
+static int scene_rebuild_axis(vf_scene* s) {
+    const float gm1 = (float)s->G - 1.0f;
+    const float step = (2.0f * 1.5f) / gm1;
+    k_axis<<<(s->G + 255) / 256, 256, 0, s->stream>>>(s->d_axis, s->G, step, gm1, s->Wd, s->Hd);
+    VF_CUDA(cudaGetLastError());
+    return VF_OK;
+}
+
+static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
+    if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "height image cannot be empty");
+    const uint32_t pitch = (w + 3u) & ~3u;            // rows start 16-byte aligned (TMA-ready)
+    if (pitch != s->pitch || h != s->Hd || !s->d_dem) {
+        VF_CUDA(cudaStreamSynchronize(s->stream));
+        cudaFree(s->d_dem);
+        s->d_dem = nullptr;
+        VF_CUDA(cudaMalloc(&s->d_dem, (size_t)pitch * h * 4));
+    }
+    s->Wd = w; s->Hd = h; s->pitch = pitch;
+    VF_CUDA(cudaMemcpy2DAsync(s->d_dem, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
+                              cudaMemcpyHostToDevice, s->stream));
+    int rc = scene_rebuild_axis(s);
+    if (rc) return rc;
+    VF_CUDA(cudaStreamSynchronize(s->stream));
+    return VF_OK;
+}
+
+extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_unorm, vf_scene** out) {
+    if (!out) return vf_set_error(VF_E_INVALID, "out is null");
+    *out = nullptr;
+    if (w <= 0 || h <= 0 || w > 16384 || h > 16384)
+        return vf_set_error(VF_E_INVALID, "width/height must be in 1..16384");
+    if (grid < 2) grid = 2;                                    // src/scene/mod.rs:61
+    if (grid > 32768) return vf_set_error(VF_E_INVALID, "grid must be <= 32768");
+    const uint8_t* pal = vf_palette_bytes(lut_id);
+    if (!pal) return vf_set_error(VF_E_INVALID, "unknown colormap id %d", lut_id);
+    int rc = vf_require_device();
+    if (rc) return rc;
+    vf_scene* s = new vf_scene();
+    memset(&s->stats, 0, sizeof s->stats);
+    memset(s->u44, 0, sizeof s->u44);
+    s->W = w; s->H = h; s->G = grid; s->lut_id = lut_id; s->lut_unorm = lut_unorm;
+    s->tiles_x = (uint32_t)(w + VF_TILE - 1) / VF_TILE;
+    s->tiles_y = (uint32_t)(h + VF_TILE - 1) / VF_TILE;
+    s->n_tiles = s->tiles_x * s->tiles_y;
+    s->n_slots = VF_MAX_SLOTS;
+#define SC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { scene_free(s); \
+        return vf_set_error(e_ == cudaErrorMemoryAllocation ? VF_E_OOM : VF_E_CUDA, \
+        "%s failed: %s", #call, cudaGetErrorString(e_)); } } while (0)
+    SC(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->own_stream = true;
+    SC(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : s->ev) SC(cudaEventCreate(&e));
+    for (auto& e : s->ev_done) SC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (auto& e : s->ev_copied) SC(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    SC(cudaMalloc(&s->d_axis, (size_t)grid * sizeof(VfAxis)));
+    SC(cudaMalloc(&s->d_lut, 256 * sizeof(float4)));
+    SC(cudaMalloc(&s->d_frame, (size_t)s->n_slots * w * h * 4));
+    SC(cudaMalloc(&s->d_tile_count, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4));
+    s->d_counters = s->d_tile_count + s->n_tiles;
+    SC(cudaMalloc(&s->d_tile_off, ((size_t)s->n_tiles + 2) * 4));
+    s->d_maxpairs = s->d_tile_off + s->n_tiles + 1;
+    SC(cudaMalloc(&s->d_tile_cursor, (size_t)s->n_tiles * 4));
+    SC(cudaHostAlloc(&s->h_counters, 64 * VF_CNT_WORDS * 4, cudaHostAllocDefault));
+#undef SC
+    float4 lut[256];
+    build_lut(pal, lut_unorm, lut);
+    cudaError_t e = cudaMemcpy(s->d_lut, lut, sizeof lut, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { scene_free(s); return vf_set_error(VF_E_CUDA, "LUT upload: %s", cudaGetErrorString(e)); }
+    const uint64_t cap = std::max<uint64_t>(1u << 20, 4ull * (uint64_t)w * (uint64_t)h);
+    rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>(cap, 1u << 30));
+    if (rc) { scene_free(s); return rc; }
+    const float zero = 0.0f;                                   // 1x1 zero image until set_height
+    rc = scene_upload_dem(s, &zero, 1, 1);
+    if (rc) { scene_free(s); return rc; }
+    *out = s;
+    return VF_OK;
+}
+
+extern "C" void vf_scene_destroy(vf_scene* s) {
+    if (!s) return;
+    cudaStreamSynchronize(s->stream);
+    scene_free(s);
+}
+
+extern "C" int vf_scene_set_height_f32(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
+    if (!s || !host) return vf_set_error(VF_E_INVALID, "null argument");
+    return scene_upload_dem(s, host, w, h);
+}
+
+extern "C" int vf_scene_set_uniforms(vf_scene* s, const float u44[44]) {
+    if (!s || !u44) return vf_set_error(VF_E_INVALID, "null argument");
+    memcpy(s->u44, u44, sizeof s->u44);
+    return VF_OK;
+}
+
+extern "C" int vf_scene_get_uniforms(const vf_scene* s, float u44[44]) {
+    if (!s || !u44) return vf_set_error(VF_E_INVALID, "null argument");
+    memcpy(u44, s->u44, sizeof s->u44);
+    return VF_OK;
+}
+
+extern "C" int vf_scene_set_mode(vf_scene* s, int mode, int depth, float h_min, float h_max) {
+    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    if (mode != VF_MODE_SHIPPED && mode != VF_MODE_NORTHSTAR)
+        return vf_set_error(VF_E_INVALID, "mode must be VF_MODE_SHIPPED or VF_MODE_NORTHSTAR");
+    if (!isfinite(h_min) || !isfinite(h_max) || !(h_min < h_max))
+        return vf_set_error(VF_E_INVALID, "min must be < max");
+    s->mode = mode; s->depth = depth ? 1 : 0; s->h_min = h_min; s->h_max = h_max;
+    return VF_OK;
+}
+
+extern "C" int vf_scene_enable_timing(vf_scene* s, int enabled) {
+    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    s->timing = enabled != 0;
+    return VF_OK;
+}
+
+extern "C" int vf_scene_last_stats(const vf_scene* s, vf_frame_stats_t* out) {
+    if (!s || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    *out = s->stats;
+    return VF_OK;
+}
+
+extern "C" int vf_scene_set_stream(vf_scene* s, void* cuda_stream) {
+    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    VF_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->own_stream) { cudaStreamDestroy(s->stream); s->own_stream = false; }
+    if (cuda_stream) s->stream = (cudaStream_t)cuda_stream;
+    else { VF_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)); s->own_stream = true; }
+    return VF_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// frame constants from the 44-float uniform block (src/terrain/mod.rs:114-142)
+static void build_frame(const vf_scene* s, const float* u, VfFrame* f) {
+    memcpy(f->V, u, 64);
+    memcpy(f->P, u + 16, 64);
+    // normalize(sun) with the contract's operation order (terrain.wgsl:83)
+    const float sx = u[32], sy = u[33], sz = u[34];
+    const float d = fmaf(sz, sz, fmaf(sx, sx, sy * sy));
+    const float r = 1.0f / sqrtf(d);
+    f->sunL[0] = sx * r; f->sunL[1] = sy * r; f->sunL[2] = sz * r;
+    f->exposure = u[35];
+    f->spacing = fmaxf(u[36], 1e-8f);                    // terrain.wgsl:46
+    f->h_range = fmaxf(u[37], 1e-8f);                    // terrain.wgsl:71
+    f->exag = u[38];
+    f->h_min = s->h_min; f->h_max = s->h_max;
+    f->gm1 = (float)s->G - 1.0f;
+    f->step = (2.0f * 1.5f) / f->gm1;
+    f->hw = 0.5f * (float)s->W; f->hh = 0.5f * (float)s->H;
+    f->G = s->G; f->W = (uint32_t)s->W; f->H = (uint32_t)s->H;
+    f->Wd = s->Wd; f->Hd = s->Hd; f->dem_pitch = s->pitch;
+    f->tiles_x = s->tiles_x; f->tiles_y = s->tiles_y;
+    f->mode = s->mode; f->depth = s->depth;
+}
+
+static uint32_t clear_rgba8() {
+    const float* thr = vf_srgb_thresholds_host();
+    auto enc = [&](float x) { uint32_t c = 0; for (int k = 1; k < 256; ++k) if (thr[k] <= x) c = k; return c; };
+    // clear colour (0.02, 0.02, 0.03, 1): src/scene/mod.rs:286
+    return enc(0.02f) | (enc(0.02f) << 8) | (enc(0.03f) << 16) | 0xff000000u;
+}
+
+// enqueue one frame into slot `slot` on s->stream
+static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vis) {
+    VfFrame f;
+    build_frame(s, u44, &f);
+    static const uint32_t clear = clear_rgba8();
+    const float* thr = vf_srgb_thresholds_dev();
+    uint8_t* frame = s->d_frame + (size_t)slot * s->W * s->H * 4;
+    VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
+    if (s->timing) VF_CUDA(cudaEventRecord(s->ev[0], s->stream));
+    const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
+    k_geom<<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
+        f, s->d_axis, s->d_dem, s->d_tile_count, s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);
+    if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
+    k_scan<<<1, 1024, 0, s->stream>>>(s->d_tile_count, s->d_tile_off, s->d_tile_cursor, s->n_tiles,
+                                      s->d_counters, s->d_maxpairs);
+    k_scatter<<<148 * 4, 256, 0, s->stream>>>(s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity,
+                                              s->d_tile_off, s->d_tile_cursor, s->d_sorted);
+    if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
+    k_raster<<<s->n_tiles, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_tile_off,
+                                                s->d_sorted, clear, frame, d_vis);
+    if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
+    VF_CUDA(cudaGetLastError());
+    return VF_OK;
+}
+
+// h_counters layout: [0..3] last frame's counters, [4] high-water mark of requested pairs
+static int scene_fetch_counters(vf_scene* s) {
+    VF_CUDA(cudaMemcpyAsync(s->h_counters, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
+    VF_CUDA(cudaMemcpyAsync(s->h_counters + 4, s->d_maxpairs, 4, cudaMemcpyDeviceToHost, s->stream));
+    return VF_OK;
+}
+
+static int scene_finish_stats(vf_scene* s) {
+    s->stats.bin_pairs = s->h_counters[VF_CNT_PAIRS];
+    s->stats.clipped_prims = s->h_counters[VF_CNT_CLIPPED];
+    s->stats.bin_capacity = s->capacity;
+    s->stats.tiles = s->n_tiles;
+    if (s->timing) {
+        VF_CUDA(cudaEventElapsedTime(&s->stats.ms_geom, s->ev[0], s->ev[1]));
+        VF_CUDA(cudaEventElapsedTime(&s->stats.ms_bin, s->ev[1], s->ev[2]));
+        VF_CUDA(cudaEventElapsedTime(&s->stats.ms_raster, s->ev[2], s->ev[3]));
+        VF_CUDA(cudaEventElapsedTime(&s->stats.ms_total, s->ev[0], s->ev[3]));
+    }
+    return VF_OK;
+}
+
+// Renders n frames; out_host may be null (frames stay on the device).  Frame k is rendered into
+// slot k%2 while the copy stream drains slot (k-1)%2 to the host.  If the binning kernel asked
+// for more pairs than the buffer holds, the buffer is grown and the whole call is repeated.
+static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis) {
+    if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    const size_t fbytes = (size_t)s->W * s->H * 4;
+    for (int attempt = 0; attempt < 8; ++attempt) {
+        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 4, s->stream));
+        for (int k = 0; k < n; ++k) {
+            const int slot = k % VF_MAX_SLOTS;
+            if (out_host && k >= VF_MAX_SLOTS) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
+            rc = scene_enqueue(s, u44xn + (size_t)k * 44, slot, d_vis);
+            if (rc) return rc;
+            if (out_host) {
+                VF_CUDA(cudaEventRecord(s->ev_done[slot], s->stream));
+                VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[slot], 0));
+                VF_CUDA(cudaMemcpyAsync(out_host + (size_t)k * fbytes, s->d_frame + (size_t)slot * fbytes,
+                                        fbytes, cudaMemcpyDeviceToHost, s->copy_stream));
+                VF_CUDA(cudaEventRecord(s->ev_copied[slot], s->copy_stream));
+            }
+        }
+        rc = scene_fetch_counters(s);
+        if (rc) return rc;
+        VF_CUDA(cudaStreamSynchronize(s->stream));
+        if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
+        const uint32_t need = s->h_counters[4];
+        if (need <= s->capacity) return scene_finish_stats(s);
+        if (need > (1u << 30)) return vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
+        const uint64_t grown = std::min<uint64_t>((uint64_t)need + need / 4 + 1024, 1u << 30);
+        rc = scene_alloc_pairs(s, (uint32_t)grown);
+        if (rc) return rc;
+    }
+    return vf_set_error(VF_E_CUDA, "pair buffer kept overflowing");
+}
+
+extern "C" int vf_scene_render_rgba(vf_scene* s, uint8_t* out_rgba_host) {
+    if (!s || !out_rgba_host) return vf_set_error(VF_E_INVALID, "null argument");
+    return scene_render(s, s->u44, 1, out_rgba_host, nullptr);
+}
+
+extern "C" int vf_scene_render_batch(vf_scene* s, const float* u44xn, int n, uint8_t* out_rgba_host) {
+    if (!s || !out_rgba_host) return vf_set_error(VF_E_INVALID, "null argument");
+    return scene_render(s, u44xn, n, out_rgba_host, nullptr);
+}
+
+extern "C" int vf_scene_render_device(vf_scene* s, const float* u44xn, int n) {
+    return scene_render(s, u44xn ? u44xn : (s ? s->u44 : nullptr), n, nullptr, nullptr);
+}
+
+extern "C" int vf_scene_debug_visibility(vf_scene* s, uint32_t* out_host) {
+    if (!s || !out_host) return vf_set_error(VF_E_INVALID, "null argument");
+    const size_t bytes = (size_t)s->W * s->H * 4;
+    if (!s->d_vis) VF_CUDA(cudaMalloc(&s->d_vis, bytes));
+    int rc = scene_render(s, s->u44, 1, nullptr, s->d_vis);
+    if (rc) return rc;
+    VF_CUDA(cudaMemcpy(out_host, s->d_vis, bytes, cudaMemcpyDeviceToHost));
+    return VF_OK;
+}
+
+// 1-99 % range of the scene's DEM (src/renderer.rs:24-28); implemented in vf_dem.cu
+int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, int clamp,
+                         float* lo, float* hi, cudaStream_t stream);
+
+extern "C" int vf_scene_auto_height_range(vf_scene* s, float* h_min, float* h_max) {
+    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    float lo, hi;
+    int rc = vf_dem_minmax_device(s->d_dem, s->Wd, s->Hd, s->pitch, 1, &lo, &hi, s->stream);
+    if (rc) return rc;
+    const float guard = lo + 1e-5f;
+    hi = hi > guard ? hi : guard;
+    s->h_min = lo; s->h_max = hi;
+    if (h_min) *h_min = lo;
+    if (h_max) *h_max = hi;
+    return VF_OK;
+}

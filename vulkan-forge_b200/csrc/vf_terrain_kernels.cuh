@@ -177,7 +177,8 @@ k_geom(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
 // exclusive prefix sum of tile_count[0..n) -> tile_off[0..n]; zeroes tile_cursor. One CTA.
 __global__ void __launch_bounds__(1024)
 k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
-       uint32_t* __restrict__ tile_cursor, uint32_t n) {
+       uint32_t* __restrict__ tile_cursor, uint32_t n, const uint32_t* __restrict__ counters,
+       uint32_t* __restrict__ max_pairs) {
     __shared__ uint32_t warp_sum[32];
     __shared__ uint32_t carry;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
@@ -214,7 +215,10 @@ k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
         if (tid == 1023) carry = c + prev_warps + incl;
         __syncthreads();
     }
-    if (tid == 0) tile_off[n] = carry;
+    if (tid == 0) {
+        tile_off[n] = carry;
+        atomicMax(max_pairs, counters[VF_CNT_PAIRS]);   // high-water mark over a batch
+    }
 }
 
 __global__ void k_scatter(const uint32_t* __restrict__ pair_tile, const uint32_t* __restrict__ pair_prim,

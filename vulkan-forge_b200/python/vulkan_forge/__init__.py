@@ -40,7 +40,8 @@ def render_triangle_rgba(width: int, height: int):
 def render_triangle_png(path, width: int, height: int) -> None:
     """Write the deterministic triangle to ``path`` (reference __init__.py:60-64)."""
     w, h = _check_size(width, height)
-    Renderer(w, h).render_triangle_png(_check_png(path))
+    target = _check_png(path)                # all argument errors surface before the device is touched
+    Renderer(w, h).render_triangle_png(target)
 
 
 def make_terrain(width: int, height: int, grid: int = 128):

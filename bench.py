@@ -1,0 +1,276 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200-native vulkan-forge render path.
+
+Workload (BASELINE.json configs[2], the one `metric` is quoted on): Scene 1920x1080, synthetic
+4096x4096 DEM (seed 0), grid 4096 (every texel a vertex), terrain LUT, NORTHSTAR shading (sun
+35/120, exposure 1.1, Reinhard, 1-99 % percentile range).  A step = FRAMES orbit frames per GPU.
+
+  value : frames/s, whole job, DEM resident in HBM, frames left in HBM (CUDA events on the launch
+          stream, L2 flushed between steps, max over ranks)
+  e2e   : frames/s through the public Python API with HOST buffers: every step uploads the DEM from
+          pinned host memory, renders, and gathers the frames into pinned host memory
+  roofline / cpu_baseline : see DESIGN.md "Measurement"
+`--impl reference` times the reference's CPU path instead: wgpu on a software adapter is
+unavailable on this box and the Rust crate cannot be built, so it is the C oracle (oracle/)
+on all host threads -- the one place besides cpu_baseline where bench.py executes oracle/.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "vulkan-forge_b200", "python"))
+
+W, H, G, DEM_N, DEM_SEED, CMAP = 1920, 1080, 4096, 4096, 0, "terrain"
+ALGO_BYTES_FRAME = 4 * min(G * G, DEM_N * DEM_N) + 4 * W * H + 1024 + 176
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            pass
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out = self.p.communicate(timeout=5)[0]
+        except Exception:
+            self.p.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def orbit_uniform_blocks(vf, scene, n, frames):
+    return scene.camera_blocks(vf.orbit_cameras(n)[:frames])
+
+
+def cpu_reference_fps(frames_budget_s, dem, uniforms, hmin, hmax, min_frames=2, max_frames=64):
+    """Reference CPU path stand-in (oracle, all host threads) on a bounded sample of the workload."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import vf_oracle as oracle
+    lut = np.fromfile(os.path.join(ROOT, "tests", "golden", f"lut_{CMAP}.rgba"), np.uint8)
+    t0 = time.perf_counter()
+    n = 0
+    while n < max_frames and (n < min_frames or time.perf_counter() - t0 < frames_budget_s):
+        oracle.render_terrain(W, H, G, dem, uniforms[n % len(uniforms)], lut, mode=oracle.MODE_NORTHSTAR, depth=False,
+                              h_min=hmin, h_max=hmax)
+        n += 1
+    dt = time.perf_counter() - t0
+    return n / dt, n, oracle.max_threads(), dt
+
+
+def run_reference(args):
+    """--impl reference: CPU only; rank 0 alone works."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import vf_oracle as oracle
+    from vulkan_forge._synthetic import synthetic_dem
+    import vulkan_forge as vf
+    dem = synthetic_dem(DEM_SEED, DEM_N)
+    hmin, hmax = (float(x) for x in oracle.h_range(dem))
+    cams = vf.orbit_cameras(max(args.frames, 1) * 4)
+    us = [oracle.look_at_uniforms(W, H, c[0], c[1], c[2], c[3], c[4], c[5], sun=oracle.sun_dir(35.0, 120.0), exposure=1.1,
+                                  h_min=hmin, h_max=hmax, normalize_sun=False) for c in cams]
+    lut = np.fromfile(os.path.join(ROOT, "tests", "golden", f"lut_{CMAP}.rgba"), np.uint8)
+    per_step = args.ref_frames
+
+    def step(k):
+        for j in range(per_step):
+            oracle.render_terrain(W, H, G, dem, us[(k * per_step + j) % len(us)], lut, mode=oracle.MODE_NORTHSTAR,
+                                  h_min=hmin, h_max=hmax)
+    for k in range(args.warmup):
+        step(k)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(k)
+    dt = time.perf_counter() - t0
+    fps = args.steps * per_step / dt
+    line = {
+        "impl": "reference", "metric": "terrain frames/s (1080p, 4096^2 DEM)", "value": fps, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "c3: Scene 1920x1080, DEM 4096^2 seed 0, grid 4096, terrain LUT, NORTHSTAR", "frames_per_step": per_step},
+        "mpix_per_s": fps * W * H / 1e6,
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": oracle.max_threads(), "kind": "port",
+                         "sample": f"{args.steps}x{per_step} frames of the same workload; oracle/ (C + OpenMP); the reference's wgpu software path is unavailable on this box"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--frames", type=int, default=8, help="frames per step per GPU")
+    ap.add_argument("--ref-frames", type=int, default=2, help="frames per step of the CPU reference arm")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline sample")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    import vulkan_forge as vf
+    from vulkan_forge._synthetic import synthetic_dem
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ext = vf._vulkan_forge
+
+    dem = torch.from_numpy(synthetic_dem(DEM_SEED, DEM_N)).pin_memory().numpy()     # pinned host input
+    sc = ext.Scene(W, H, grid=G, colormap=CMAP)
+    stream = torch.cuda.Stream()
+    sc.set_stream(stream.cuda_stream)
+    sc.set_height_from_r32f(dem)
+    sc.set_shading("northstar", depth=False)
+    sc.set_sun(35.0, 120.0)
+    sc.set_exposure(1.1)
+    hmin, hmax = sc.set_auto_height_range()
+    F = args.frames
+    n_orbit = F * max(world, 1) * 4
+    lo = (rank * F) % n_orbit
+    blocks = sc.camera_blocks(vf.orbit_cameras(n_orbit)[lo:lo + F])                  # each rank its own cameras
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")                 # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- value: device-resident ----
+    for _ in range(args.warmup):
+        sc.render_batch_device(blocks)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    with torch.cuda.stream(stream):
+        for k in range(args.steps):
+            flush.zero_()                                                            # L2 flush, outside the events
+            ev[k][0].record(stream)
+            sc.render_batch_device(blocks)
+            ev[k][1].record(stream)
+    barrier()
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if sampler else None
+
+    # per-kernel times of one frame (CUDA events inside the library, same stream), L2 flushed
+    sc.enable_timing(True)
+    kt = {"ms_geom": [], "ms_bin": [], "ms_raster": [], "ms_total": []}
+    for k in range(max(5, args.warmup)):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        sc.render_batch_device(blocks[k % F:k % F + 1])
+        m = sc.render_metrics()
+        for key in kt:
+            kt[key].append(m[key])
+    sc.enable_timing(False)
+    kmed = {k: statistics.median(v) for k, v in kt.items()}
+
+    # ---- e2e: public API, host buffers, H2D + D2H inside the timed region ----
+    def e2e_step():
+        sc.set_height_from_r32f(dem)                       # 64 MiB H2D from pinned memory
+        frames = sc.render_batch_rgba(blocks)              # (F,H,W,4) gathered into pinned host memory
+        return int(frames[:, ::270, ::480, :3].sum())      # device->host result actually read
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+
+    t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_s = float(t[0]), float(t[1])
+    total_frames = args.steps * F * world
+    fps = total_frames / (dev_ms / 1e3)
+    e2e_fps = total_frames / e2e_s
+
+    if rank == 0:
+        peak, peak_kind = peaks()
+        dom = max(("ms_geom", "ms_bin", "ms_raster"), key=lambda k: kmed[k])
+        algo = {"ms_geom": 4 * G * G + 16 * G + 176, "ms_bin": 0, "ms_raster": 4 * W * H + 1024 + 176}
+        dom_bytes = algo[dom] if algo[dom] else ALGO_BYTES_FRAME
+        achieved = dom_bytes / (kmed[dom] * 1e-3) / 1e9
+        frame_achieved = ALGO_BYTES_FRAME / (kmed["ms_total"] * 1e-3) / 1e9
+        cpu = None
+        if world == 1 or rank == 0:
+            us = [np.asarray(blocks[i]) for i in range(min(F, 4))]
+            cfps, cn, cores, cdt = cpu_reference_fps(args.cpu_seconds, dem, us, float(hmin), float(hmax))
+            cpu = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",
+                   "sample": f"{cn} frames of the same workload in {cdt:.1f} s; oracle/ (C + OpenMP, all host threads)"}
+        line = {
+            "metric": "terrain frames/s (1080p, 4096^2 DEM)", "value": fps, "unit": "frames/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "c3: Scene 1920x1080, DEM 4096^2 seed 0, grid 4096, terrain LUT, NORTHSTAR (sun 35/120, exposure 1.1, auto 1-99%)",
+                       "frames_per_step_per_gpu": F, "l2": "flushed between steps (256 MiB write)", "sharding": "independent frames per GPU, no collective"},
+            "mpix_per_s": fps * W * H / 1e6,
+            "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
+                    "mpix_per_s": e2e_fps * W * H / 1e6},
+            "gpu_launches": args.steps * F * 4,
+            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom", "ms_bin": "k_scan+k_scatter", "ms_raster": "k_raster"}[dom],
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kmed[dom],
+                         "frame": {"algorithmic_bytes": ALGO_BYTES_FRAME, "ms": kmed["ms_total"], "achieved": frame_achieved, "frac": frame_achieved / peak},
+                         "kernels_ms": kmed},
+            "cpu_baseline": cpu,
+            "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -85,18 +85,36 @@ def test_non_square_dem_and_ragged_rows(ext, oracle, luts, synthetic_dem):
 
 def test_near_plane_clipping_path(ext, oracle, luts, synthetic_dem):
     dem = synthetic_dem(6, 64) * np.float32(0.2)
-    cam = ((0.2, 0.08, 0.4), (1.5, 0.0, 1.2), (0.0, 1.0, 0.0), 70.0, 0.1, 100.0)
+    cam = ((0.0, 0.15, 0.0), (1.0, 0.0, 1.0), (0.0, 1.0, 0.0), 90.0, 0.1, 100.0)   # eye just above the surface
     for mode, depth in (("northstar", True), ("shipped", False)):
         sc, got, ref, gvis, rvis = _render_both(ext, oracle, luts, 400, 300, 64, dem, "viridis", mode, depth, cam=cam)
         assert sc.render_metrics()["clipped_prims"] > 0, "camera did not exercise the Sutherland-Hodgman path"
         _check(got, ref, gvis, rvis, mode)
 
 
-def test_far_plane_and_guard_band(ext, oracle, luts, synthetic_dem):
+def _correct_projection_uniforms(oracle, W, H, eye, tgt, fovy, zn, zf):
+    """The shipped gl_to_wgpu is transposed (src/camera.rs:14-21), which makes z <= w always true, so
+    the far plane can only be reached with a correct [0,1]-depth projection supplied as raw uniforms."""
+    D = np.array([[1, 0, 0, 0], [0, 1, 0, 0], [0, 0, .5, .5], [0, 0, 0, 1]], np.float32)
+    return oracle.uniforms(oracle.look_at(eye, tgt, (0, 1, 0)), D @ oracle.perspective(fovy, W / H, zn, zf, "gl"))
+
+
+@pytest.mark.parametrize("tag,G,cam", [
+    ("far plane cuts the terrain", 48, ((1.4, 0.6, 1.4), (-1.5, 0.0, -1.5), 100.0, 0.05, 2.0)),
+    ("guard band: huge triangles, 5 degree lens", 2, ((0.0, 2.0, 0.0), (0.3, 0.0, 0.3), 5.0, 0.1, 100.0)),
+])
+def test_far_plane_and_guard_band(ext, oracle, luts, synthetic_dem, tag, G, cam):
     dem = synthetic_dem(7, 64)
-    cam = ((1.4, 0.6, 1.4), (-1.5, 0.0, -1.5), (0.0, 1.0, 0.0), 100.0, 0.05, 2.0)   # far plane cuts the terrain
-    sc, got, ref, gvis, rvis = _render_both(ext, oracle, luts, 320, 200, 48, dem, "magma", "northstar", True, cam=cam)
-    assert sc.render_metrics()["clipped_prims"] > 0
+    W, H = 320, 200
+    u = _correct_projection_uniforms(oracle, W, H, *cam)
+    sc = ext.Scene(W, H, grid=G, colormap="magma")
+    sc.set_height_from_r32f(dem)
+    sc.set_shading("northstar", depth=True)
+    sc.set_uniforms_raw(u)
+    got, gvis = sc.render_rgba(), sc.debug_visibility()
+    ref, rvis, cnt = oracle.render_terrain(W, H, G, dem, u, luts["magma"], mode=oracle.MODE_NORTHSTAR, depth=True,
+                                           want_prim=True, want_counters=True)
+    assert cnt["tris_clipped"] > 0 and sc.render_metrics()["clipped_prims"] == cnt["tris_clipped"], tag
     _check(got, ref, gvis, rvis, "northstar")
 
 
@@ -105,11 +123,11 @@ def test_draw_order_resolve_without_depth(ext, oracle, luts):
     triangles overlap, the one drawn LAST (highest primitive id) wins; with depth the nearest wins."""
     n = 64
     yy, xx = np.mgrid[0:n, 0:n]
-    dem = (0.6 * np.exp(-((xx - 40) ** 2 + (yy - 24) ** 2) / 40.0)).astype(np.float32)   # a spike that self-occludes
+    dem = (1.5 * np.exp(-((xx - 40) ** 2 + (yy - 24) ** 2) / 40.0)).astype(np.float32)   # a spike that self-occludes
     res = {}
     for depth in (False, True):
         _, got, ref, gvis, rvis = _render_both(ext, oracle, luts, 320, 240, n, dem, "viridis", "northstar", depth, auto=False,
-                                               cam=((3.0, 0.6, 0.5), (0, 0.1, 0), (0, 1, 0), 40.0, 0.1, 100.0))
+                                               cam=((3.0, 0.2, -2.0), (0, 0.3, 0), (0, 1, 0), 40.0, 0.1, 100.0))
         _check(got, ref, gvis, rvis, "northstar")
         res[depth] = gvis
     differ = res[False] != res[True]

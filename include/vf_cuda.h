@@ -55,6 +55,7 @@ typedef struct {
     uint32_t bin_capacity;   /* capacity of the pair buffer (grown automatically) */
     uint32_t clipped_prims;  /* primitives that took the Sutherland-Hodgman path */
     uint32_t tiles;          /* screen tiles (16x16 px) */
+    uint32_t big_prims;      /* primitives routed to the binned path (large or clipped) */
     float ms_geom, ms_bin, ms_raster, ms_total; /* CUDA-event times, only when timing enabled */
 } vf_frame_stats_t;
 

@@ -12,4 +12,7 @@ sc.set_height_from_r32f(synthetic_dem(0, 4096))
 if mode == "northstar":
     sc.set_shading("northstar", depth=False); sc.set_sun(35.0, 120.0); sc.set_exposure(1.1); sc.set_auto_height_range()
 ms = sc.render_batch_device(vf.orbit_cameras(32)[:n])
-print("frames", n, "ms", ms, sc.render_metrics())
+print("frames", n, "ms", round(ms, 3), "ms/frame", round(ms / n, 4))
+sc.enable_timing(True)
+sc.render_batch_device(vf.orbit_cameras(32)[:1])
+print({k: (round(v, 4) if isinstance(v, float) else v) for k, v in sc.render_metrics().items()})

@@ -27,8 +27,11 @@ struct vf_scene {
     uint32_t tiles_x = 0, tiles_y = 0, n_tiles = 0;
     uint32_t* d_tile_count = nullptr;    // [n_tiles] counts | [VF_CNT_WORDS] counters (one memset)
     uint32_t* d_counters = nullptr;      // = d_tile_count + n_tiles
-    uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [1] high-water mark of pairs
+    uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [2] high-water marks (pairs, queued prims)
     uint32_t* d_maxpairs = nullptr;      // = d_tile_off + n_tiles + 1
+    unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
+    int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
+    uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
     uint32_t* d_pair_tile = nullptr; uint32_t* d_pair_prim = nullptr; uint32_t* d_sorted = nullptr;
     uint32_t capacity = 0;
@@ -48,7 +51,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_dem); cudaFree(s->d_axis); cudaFree(s->d_lut); cudaFree(s->d_frame);
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
-    cudaFree(s->d_sorted);
+    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -66,6 +69,14 @@ static int scene_alloc_pairs(vf_scene* s, uint32_t capacity) {
     VF_CUDA(cudaMalloc(&s->d_pair_prim, (size_t)capacity * 4));
     VF_CUDA(cudaMalloc(&s->d_sorted, (size_t)capacity * 4));
     s->capacity = capacity;
+    return VF_OK;
+}
+
+static int scene_alloc_big(vf_scene* s, uint32_t capacity) {
+    cudaFree(s->d_big);
+    s->d_big = nullptr;
+    VF_CUDA(cudaMalloc(&s->d_big, (size_t)capacity * 4));
+    s->big_capacity = capacity;
     return VF_OK;
 }
 
@@ -121,8 +132,8 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
 extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_unorm, vf_scene** out) {
     if (!out) return vf_set_error(VF_E_INVALID, "out is null");
     *out = nullptr;
-    if (w <= 0 || h <= 0 || w > 16384 || h > 16384)
-        return vf_set_error(VF_E_INVALID, "width/height must be in 1..16384");
+    if (w <= 0 || h <= 0 || w > 8192 || h > 8192)   // 8192: python/vulkan_forge/_validate.py:6; keeps |X| < 2^24
+        return vf_set_error(VF_E_INVALID, "width/height must be in 1..8192");
     if (grid < 2) grid = 2;                                    // src/scene/mod.rs:61
     if (grid > 32768) return vf_set_error(VF_E_INVALID, "grid must be <= 32768");
     const uint8_t* pal = vf_palette_bytes(lut_id);
@@ -151,7 +162,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     SC(cudaMalloc(&s->d_frame, (size_t)s->n_slots * w * h * 4));
     SC(cudaMalloc(&s->d_tile_count, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4));
     s->d_counters = s->d_tile_count + s->n_tiles;
-    SC(cudaMalloc(&s->d_tile_off, ((size_t)s->n_tiles + 2) * 4));
+    SC(cudaMalloc(&s->d_tile_off, ((size_t)s->n_tiles + 3) * 4));
     s->d_maxpairs = s->d_tile_off + s->n_tiles + 1;
     SC(cudaMalloc(&s->d_tile_cursor, (size_t)s->n_tiles * 4));
     SC(cudaHostAlloc(&s->h_counters, 64 * VF_CNT_WORDS * 4, cudaHostAllocDefault));
@@ -163,6 +174,13 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     const uint64_t cap = std::max<uint64_t>(1u << 20, 4ull * (uint64_t)w * (uint64_t)h);
     rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>(cap, 1u << 30));
     if (rc) { scene_free(s); return rc; }
+    rc = scene_alloc_big(s, 1u << 20);
+    if (rc) { scene_free(s); return rc; }
+    if (cudaMalloc(&s->d_visbuf, (size_t)w * h * 8) != cudaSuccess) {
+        scene_free(s);
+        (void)cudaGetLastError();
+        return vf_set_error(VF_E_OOM, "visibility buffer allocation failed");
+    }
     const float zero = 0.0f;                                   // 1x1 zero image until set_height
     rc = scene_upload_dem(s, &zero, 1, 1);
     if (rc) { scene_free(s); return rc; }
@@ -264,16 +282,22 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     uint8_t* frame = s->d_frame + (size_t)slot * s->W * s->H * 4;
     VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[0], s->stream));
+    if (s->visbuf_depth != f.depth) {     // (re)initialise the self-cleaning visibility buffer
+        VF_CUDA(cudaMemsetAsync(s->d_visbuf, f.depth ? 0xff : 0x00, (size_t)s->W * s->H * 8, s->stream));
+        s->visbuf_depth = f.depth;
+    }
     const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
     k_geom<<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
-        f, s->d_axis, s->d_dem, s->d_tile_count, s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);
+        f, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
+    k_bin<<<148 * 2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_big, s->big_capacity, s->d_tile_count,
+                                          s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);
     k_scan<<<1, 1024, 0, s->stream>>>(s->d_tile_count, s->d_tile_off, s->d_tile_cursor, s->n_tiles,
                                       s->d_counters, s->d_maxpairs);
     k_scatter<<<148 * 4, 256, 0, s->stream>>>(s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity,
                                               s->d_tile_off, s->d_tile_cursor, s->d_sorted);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
-    k_raster<<<s->n_tiles, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_tile_off,
+    k_raster<<<s->n_tiles, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
                                                 s->d_sorted, clear, frame, d_vis);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());
@@ -283,7 +307,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
 // h_counters layout: [0..3] last frame's counters, [4] high-water mark of requested pairs
 static int scene_fetch_counters(vf_scene* s) {
     VF_CUDA(cudaMemcpyAsync(s->h_counters, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
-    VF_CUDA(cudaMemcpyAsync(s->h_counters + 4, s->d_maxpairs, 4, cudaMemcpyDeviceToHost, s->stream));
+    VF_CUDA(cudaMemcpyAsync(s->h_counters + 4, s->d_maxpairs, 8, cudaMemcpyDeviceToHost, s->stream));
     return VF_OK;
 }
 
@@ -291,6 +315,7 @@ static int scene_finish_stats(vf_scene* s) {
     s->stats.bin_pairs = s->h_counters[VF_CNT_PAIRS];
     s->stats.clipped_prims = s->h_counters[VF_CNT_CLIPPED];
     s->stats.bin_capacity = s->capacity;
+    s->stats.big_prims = s->h_counters[VF_CNT_BIG];
     s->stats.tiles = s->n_tiles;
     if (s->timing) {
         VF_CUDA(cudaEventElapsedTime(&s->stats.ms_geom, s->ev[0], s->ev[1]));
@@ -310,7 +335,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
     if (rc) return rc;
     const size_t fbytes = (size_t)s->W * s->H * 4;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 4, s->stream));
+        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 8, s->stream));
         for (int k = 0; k < n; ++k) {
             const int slot = k % VF_MAX_SLOTS;
             if (out_host && k >= VF_MAX_SLOTS) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
@@ -328,12 +353,19 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         if (rc) return rc;
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
-        const uint32_t need = s->h_counters[4];
-        if (need <= s->capacity) return scene_finish_stats(s);
+        const uint32_t need = s->h_counters[4], need_big = s->h_counters[5];
+        if (need <= s->capacity && need_big <= s->big_capacity) return scene_finish_stats(s);
+        // an overflowed frame left stale keys in the visibility buffer only if k_raster did not run
+        // to completion; it always does, so the buffer is clean and the call can simply be repeated
         if (need > (1u << 30)) return vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
-        const uint64_t grown = std::min<uint64_t>((uint64_t)need + need / 4 + 1024, 1u << 30);
-        rc = scene_alloc_pairs(s, (uint32_t)grown);
-        if (rc) return rc;
+        if (need > s->capacity) {
+            rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>((uint64_t)need + need / 4 + 1024, 1u << 30));
+            if (rc) return rc;
+        }
+        if (need_big > s->big_capacity) {
+            rc = scene_alloc_big(s, need_big + need_big / 4 + 1024);
+            if (rc) return rc;
+        }
     }
     return vf_set_error(VF_E_CUDA, "pair buffer kept overflowing");
 }

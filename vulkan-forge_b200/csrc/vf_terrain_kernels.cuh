@@ -1,11 +1,18 @@
-// vf_terrain_kernels.cuh -- the terrain frame as four sm_100a kernels:
+// vf_terrain_kernels.cuh -- the terrain frame on sm_100a.
+//
 //   k_axis    : per-index tables of the implicit grid (x|z, u|v, texel column/row)
-//   k_geom    : vertex stage + cull + tile binning (warp-scan compaction)      [dominant]
-//   k_scan / k_scatter : per-tile prefix sum and scatter of (tile, primitive) pairs
-//   k_raster  : per-tile coverage (integer edge functions, top-left), on-chip visibility /
-//               depth resolve, fused fragment stage, sRGB encode, 16-byte RGBA8 stores
+//   k_geom    : vertex stage once per vertex (smem), hierarchical cull (quad bbox -> triangle),
+//               MICRO triangles (bbox <= VF_MICRO_MAX pixel centres, no clipping) are rasterised
+//               on the spot into the L2-resident visibility buffer with one atomic per covered
+//               sample; everything else (large or clipped primitives) goes to a queue      [dominant]
+//   k_bin     : queue -> (tile, primitive) pairs, warp-scan compaction
+//   k_scan / k_scatter : per-tile prefix sum and scatter
+//   k_raster  : per 16x16 tile: merges the visibility buffer with the tile's binned primitives in
+//               shared memory (integer edge functions, top-left rule, last-drawn-wins or depth
+//               Less), then the fused fragment stage, exact sRGB8 and 16-byte RGBA8 stores
 // replaces: vs_main/fs_main of src/shaders/terrain.wgsl and the fixed-function state of
-// src/terrain/pipeline.rs:107-140 (see DESIGN.md for the data layout and rooflines).
+// src/terrain/pipeline.rs:107-140.  Results are independent of scheduling: visibility is a max
+// over primitive ids (no depth) or a min over (depth, id) keys (depth), both order-free.
 #pragma once
 #include "vf_device.cuh"
 
@@ -16,9 +23,11 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_GEOM_THREADS 256
 #define VF_GEOM_VX (VF_GEOM_TX + 1)
 #define VF_GEOM_VY (VF_GEOM_TY + 1)
+#define VF_MICRO_MAX 4         // pixel-centre count up to which one thread rasterises a triangle
+#define VF_MEDIUM_MAX 4096     // ... up to which one warp does (lanes stride over the bbox); larger -> binned
 
-// counters[0] = pairs requested, [1] = clipped primitives, [2] = pairs stored
-enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_WORDS = 4 };
+// counter block (cleared per frame together with the tile counts)
+enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_WORDS = 4 };
 
 // ---------------------------------------------------------------------------------------
 __global__ void k_axis(VfAxis* __restrict__ axis, uint32_t G, float step, float gm1,
@@ -50,43 +59,94 @@ __device__ __forceinline__ void vf_prim_vertices(const VfFrame& f, const VfAxis*
     for (int k = 0; k < 3; ++k) vf_grid_vertex(f, axis, dem, ij[k][0], ij[k][1], tri[k]);
 }
 
-// ---------------------------------------------------------------------------------------
-// k_geom: one CTA = 32x32 cells (33x33 vertices).  Phase 1 transforms the vertices once and
-// keeps only what culling needs in shared memory (snapped XY + clip flags); phase 2 gives every
-// thread 4 cells (8 triangles), rejects triangles that are outside, back-facing or contain no
-// pixel centre, and appends (tile, primitive) pairs for the survivors with one atomic per warp.
-struct VfGeomSmem {
-    int2 xy[VF_GEOM_VY][VF_GEOM_VX];
-    uint8_t fl[VF_GEOM_VY][VF_GEOM_VX + 3];
-};
-
-// Tile range of one triangle in the fast path.  Returns false if culled.
-__device__ __forceinline__ bool vf_tri_tiles_fast(const VfFrame& f, int2 p0, int2 p1, int2 p2,
-                                                  int& tx0, int& tx1, int& ty0, int& ty1) {
-    int x0, x1, y0, y1;
-    const int32_t mnx = min(p0.x, min(p1.x, p2.x)), mxx = max(p0.x, max(p1.x, p2.x));
-    const int32_t mny = min(p0.y, min(p1.y, p2.y)), mxy = max(p0.y, max(p1.y, p2.y));
-    if (!vf_bbox_pixels(mnx, mxx, mny, mxy, f.W, f.H, x0, x1, y0, y1)) return false;
-    const int64_t area2 = (int64_t)(p1.x - p0.x) * (p2.y - p0.y) - (int64_t)(p1.y - p0.y) * (p2.x - p0.x);
-    if (area2 >= 0) return false;                              // cull Back / degenerate
-    tx0 = x0 / VF_TILE; tx1 = x1 / VF_TILE; ty0 = y0 / VF_TILE; ty1 = y1 / VF_TILE;
-    return true;
+// visibility resolve on one sample (global or shared memory)
+__device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool depth, uint32_t prim, float zf) {
+    if (depth) atomicMin(key64, ((unsigned long long)__float_as_uint(zf) << 32) | prim);
+    else atomicMax(reinterpret_cast<uint32_t*>(key64), prim + 1u);   // low word (little endian)
 }
 
-__global__ void __launch_bounds__(VF_GEOM_THREADS)
+// ---------------------------------------------------------------------------------------
+// Warp-cooperative rasterisation of one triangle.  Small bboxes: lanes stride over the pixel
+// centres of the bbox.  Large bboxes (needles next to DEM outliers: hundreds of pixels long, a
+// fraction of a pixel wide): lanes take the scanlines of the longer bbox axis, bound the
+// covered interval on each with a conservative float evaluation of the three edge functions
+// (margin 2/256 px; the numerators are exact int64) and run the exact integer coverage test only
+// on the pixel centres inside it.  Coverage decisions are always the exact test's.
+template <typename Emit>
+__device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1, int y0, int y1,
+                                               uint32_t lane, Emit&& emit) {
+    const uint32_t bw = (uint32_t)(x1 - x0 + 1), bh = (uint32_t)(y1 - y0 + 1), npx = bw * bh;
+    if (npx <= 64u) {
+        for (uint32_t idx = lane; idx < npx; idx += 32u) {
+            const uint32_t ry = idx / bw;
+            const int px = x0 + (int)(idx - ry * bw), py = y0 + (int)ry;
+            int64_t ed[3];
+            if (vf_covers(t, px, py, ed)) emit(px, py, ed);
+        }
+        return;
+    }
+    const bool rows = bh >= bw;                      // scanlines along the longer axis
+    const int m0 = rows ? y0 : x0, m1 = rows ? y1 : x1;      // major range (pixels)
+    const int n0 = rows ? x0 : y0, n1 = rows ? x1 : y1;      // minor range (pixels)
+    // per edge: e = cu * (minor - ou) + ck * (major - ok)
+    float cu[3], ou[3];
+    int32_t ck[3], ok[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const VfSVtx& a = t.v[(i + 1) % 3];
+        const VfSVtx& b = t.v[(i + 2) % 3];
+        const int32_t A = b.Y - a.Y, B = -(b.X - a.X);
+        cu[i] = (float)(rows ? A : B);
+        ck[i] = rows ? B : A;
+        ou[i] = (float)(rows ? a.X : a.Y);
+        ok[i] = rows ? a.Y : a.X;
+    }
+    for (int mj = m0 + (int)lane; mj <= m1; mj += 32) {
+        const int32_t sm = mj * VF_SUBPIX + VF_HALFPIX;
+        float lo = (float)(n0 * VF_SUBPIX + VF_HALFPIX), hi = (float)(n1 * VF_SUBPIX + VF_HALFPIX);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (cu[i] != 0.0f) {
+                const float v = ou[i] - (float)((int64_t)ck[i] * (int64_t)(sm - ok[i])) / cu[i];
+                if (cu[i] > 0.0f) lo = fmaxf(lo, v); else hi = fminf(hi, v);
+            }
+        }
+        int c0 = (int)ceilf((lo - (float)(VF_HALFPIX + 2)) * (1.0f / VF_SUBPIX));
+        int c1 = (int)floorf((hi - (float)(VF_HALFPIX - 2)) * (1.0f / VF_SUBPIX));
+        c0 = max(c0, n0); c1 = min(c1, n1);
+        for (int c = c0; c <= c1; ++c) {
+            const int px = rows ? c : mj, py = rows ? mj : c;
+            int64_t ed[3];
+            if (vf_covers(t, px, py, ed)) emit(px, py, ed);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+struct VfGeomSmem {
+    int2 xy[VF_GEOM_VY][VF_GEOM_VX];          // snapped screen position (valid when fl & 64)
+    float zn[VF_GEOM_VY][VF_GEOM_VX];         // z/w
+    uint8_t fl[VF_GEOM_VY][VF_GEOM_VX + 3];   // clip flags
+    uint16_t queue[VF_GEOM_TX * VF_GEOM_TY];  // cells that survived the quad-level cull
+    uint16_t mqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // triangles for the warp-cooperative rasteriser
+    uint32_t qcount, mcount;
+};
+
+__global__ void __launch_bounds__(VF_GEOM_THREADS, 4)
 k_geom(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
-       const float* __restrict__ dem, uint32_t* __restrict__ tile_count,
-       uint32_t* __restrict__ pair_tile, uint32_t* __restrict__ pair_prim,
-       uint32_t* __restrict__ counters, uint32_t capacity) {
+       const float* __restrict__ dem, unsigned long long* __restrict__ vis,
+       uint32_t* __restrict__ big_prims, uint32_t big_capacity, uint32_t* __restrict__ counters) {
     __shared__ VfGeomSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t i0 = blockIdx.x * VF_GEOM_TX, j0 = blockIdx.y * VF_GEOM_TY;
+    if (tid == 0) { sm.qcount = 0u; sm.mcount = 0u; }
 
-    // ---- phase 1: vertices ----
+    // ---- phase 1: every vertex of the 33x33 block once ----
     for (uint32_t v = tid; v < VF_GEOM_VX * VF_GEOM_VY; v += VF_GEOM_THREADS) {
         const uint32_t lj = v / VF_GEOM_VX, li = v - lj * VF_GEOM_VX;
         const uint32_t i = i0 + li, j = j0 + lj;
         int2 xy = make_int2(0, 0);
+        float zn = 0.0f;
         uint32_t fl = 63u;
         if (i < f.G && j < f.G) {
             VfVtx o;
@@ -96,94 +156,223 @@ k_geom(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
                 VfSVtx s;
                 vf_to_screen(f, o, s);
                 xy = make_int2(s.X, s.Y);
+                zn = s.zn;
             }
         }
         sm.xy[lj][li] = xy;
+        sm.zn[lj][li] = zn;
         sm.fl[lj][li] = (uint8_t)fl;
     }
     __syncthreads();
 
-    // ---- phase 2: cells ----
+    // ---- phase 2: quad-level cull (one test for two triangles) ----
     const uint32_t li = tid & 31u;
 #pragma unroll 1
     for (uint32_t r = 0; r < VF_GEOM_TY / (VF_GEOM_THREADS / 32); ++r) {
         const uint32_t lj = (tid >> 5) + r * (VF_GEOM_THREADS / 32);
-        const uint32_t i = i0 + li, j = j0 + lj;
-        const bool valid = (i + 1 < f.G) && (j + 1 < f.G);
-        const int2 pa = sm.xy[lj][li], pb = sm.xy[lj][li + 1];
-        const int2 pc = sm.xy[lj + 1][li], pd = sm.xy[lj + 1][li + 1];
-        const uint32_t fa = sm.fl[lj][li], fb = sm.fl[lj][li + 1];
-        const uint32_t fc = sm.fl[lj + 1][li], fd = sm.fl[lj + 1][li + 1];
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const uint32_t prim = 2u * (j * (f.G - 1u) + i) + (uint32_t)k;
-            const uint32_t f0 = k == 0 ? fa : fb, f1 = fc, f2 = k == 0 ? fb : fd;
-            const int2 p0 = k == 0 ? pa : pb, p1 = pc, p2 = k == 0 ? pb : pd;
-            int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-            bool live = false;
-            if (valid && !(f0 & f1 & f2 & 63u)) {
-                if (f0 & f1 & f2 & 64u) {
-                    live = vf_tri_tiles_fast(f, p0, p1, p2, tx0, tx1, ty0, ty1);
+        bool keep = (i0 + li + 1 < f.G) && (j0 + lj + 1 < f.G);
+        if (keep) {
+            const uint32_t fa = sm.fl[lj][li], fb = sm.fl[lj][li + 1];
+            const uint32_t fc = sm.fl[lj + 1][li], fd = sm.fl[lj + 1][li + 1];
+            const uint32_t fand = fa & fb & fc & fd;
+            if (fand & 63u) {
+                keep = false;                               // all four outside one frustum plane
+            } else if (fand & 64u) {
+                const int2 pa = sm.xy[lj][li], pb = sm.xy[lj][li + 1];
+                const int2 pc = sm.xy[lj + 1][li], pd = sm.xy[lj + 1][li + 1];
+                int x0, x1, y0, y1;                         // no pixel centre in the quad's bbox ->
+                keep = vf_bbox_pixels(min(min(pa.x, pb.x), min(pc.x, pd.x)), max(max(pa.x, pb.x), max(pc.x, pd.x)),
+                                      min(min(pa.y, pb.y), min(pc.y, pd.y)), max(max(pa.y, pb.y), max(pc.y, pd.y)),
+                                      f.W, f.H, x0, x1, y0, y1);   // neither triangle can cover a sample
+            }
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, keep);
+        if (m) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&sm.qcount, (uint32_t)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (keep) sm.queue[base + __popc(m & ((1u << lane) - 1u))] = (uint16_t)(lj * VF_GEOM_TX + li);
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 3: surviving triangles, densely packed over the CTA ----
+    const uint32_t n_entries = 2u * sm.qcount;
+    const bool depth = f.depth != 0;
+    for (uint32_t base = 0; base < n_entries; base += VF_GEOM_THREADS) {
+        const uint32_t e = base + tid;
+        bool to_big = false, to_med = false;
+        uint32_t prim = 0;
+        if (e < n_entries) {
+            const uint32_t q = sm.queue[e >> 1], k = e & 1u;
+            const uint32_t qj = q / VF_GEOM_TX, qi = q - qj * VF_GEOM_TX;
+            prim = 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
+            // T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
+            const uint32_t ai = k ? qi + 1 : qi, aj = qj;          // v0
+            const uint32_t bi = qi, bj = qj + 1;                   // v1 = c
+            const uint32_t ci = qi + 1, cj = k ? qj + 1 : qj;      // v2
+            const uint32_t f0 = sm.fl[aj][ai], f1 = sm.fl[bj][bi], f2 = sm.fl[cj][ci];
+            if (!(f0 & f1 & f2 & 63u)) {
+                if (!(f0 & f1 & f2 & 64u)) {
+                    to_big = true;                                  // needs clipping
                 } else {
-                    // clip path: redo the vertex stage (clip coordinates were not kept)
-                    VfVtx tri[3];
-                    vf_prim_vertices(f, axis, dem, prim, tri);
-                    int bx0 = 1 << 30, bx1 = -1, by0 = 1 << 30, by1 = -1;
-                    const bool clipped = vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
-                        int x0, x1, y0, y1;
-                        if (vf_area2(t) >= 0) return;
-                        if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
-                        bx0 = min(bx0, x0); bx1 = max(bx1, x1);
-                        by0 = min(by0, y0); by1 = max(by1, y1);
-                    });
-                    if (clipped) atomicAdd(&counters[VF_CNT_CLIPPED], 1u);
-                    if (bx1 >= bx0 && by1 >= by0) {
-                        live = true;
-                        tx0 = bx0 / VF_TILE; tx1 = bx1 / VF_TILE;
-                        ty0 = by0 / VF_TILE; ty1 = by1 / VF_TILE;
+                    VfSubTri t;
+                    t.v[0].X = sm.xy[aj][ai].x; t.v[0].Y = sm.xy[aj][ai].y; t.v[0].zn = sm.zn[aj][ai];
+                    t.v[1].X = sm.xy[bj][bi].x; t.v[1].Y = sm.xy[bj][bi].y; t.v[1].zn = sm.zn[bj][bi];
+                    t.v[2].X = sm.xy[cj][ci].x; t.v[2].Y = sm.xy[cj][ci].y; t.v[2].zn = sm.zn[cj][ci];
+                    int x0, x1, y0, y1;
+                    if (vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1) && vf_area2(t) < 0) {
+                        const int npx = (x1 - x0 + 1) * (y1 - y0 + 1);
+                        if (npx > VF_MEDIUM_MAX) {
+                            to_big = true;
+                        } else if (npx > VF_MICRO_MAX) {
+                            to_med = true;
+                        } else {
+                            for (int py = y0; py <= y1; ++py)
+                                for (int px = x0; px <= x1; ++px) {
+                                    int64_t ed[3];
+                                    if (!vf_covers(t, px, py, ed)) continue;
+                                    float zf = 0.0f;
+                                    if (depth) {
+                                        float b[3];
+                                        vf_barycentric(ed, b);
+                                        zf = vf_depth_at(t, b);
+                                        if (!(zf < 1.0f)) continue;
+                                    }
+                                    vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
+                                }
+                        }
                     }
                 }
             }
-            // ---- warp-aggregated append of (tile, prim) pairs ----
-            const uint32_t nt = live ? (uint32_t)((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) : 0u;
-            if (__ballot_sync(0xffffffffu, nt != 0u) == 0u) continue;
-            uint32_t incl = nt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= (uint32_t)d) incl += t;
-            }
-            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(&counters[VF_CNT_PAIRS], total);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            uint32_t pos = base + incl - nt;
-            if (nt) {
-                for (int ty = ty0; ty <= ty1; ++ty)
-                    for (int tx = tx0; tx <= tx1; ++tx, ++pos) {
-                        if (pos < capacity) {
-                            const uint32_t tile = (uint32_t)ty * f.tiles_x + (uint32_t)tx;
-                            pair_tile[pos] = tile;
-                            pair_prim[pos] = prim;
-                            atomicAdd(&tile_count[tile], 1u);
-                        }
-                    }
-            }
         }
+        const uint32_t mm = __ballot_sync(0xffffffffu, to_med);
+        if (mm) {
+            uint32_t mb = 0;
+            if (lane == 0) mb = atomicAdd(&sm.mcount, (uint32_t)__popc(mm));
+            mb = __shfl_sync(0xffffffffu, mb, 0);
+            if (to_med) sm.mqueue[mb + __popc(mm & ((1u << lane) - 1u))] = (uint16_t)(((e >> 1) << 1) | (e & 1u));
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, to_big);
+        if (m) {
+            uint32_t gb = 0;
+            if (lane == 0) gb = atomicAdd(&counters[VF_CNT_BIG], (uint32_t)__popc(m));
+            gb = __shfl_sync(0xffffffffu, gb, 0);
+            const uint32_t pos = gb + __popc(m & ((1u << lane) - 1u));
+            if (to_big && pos < big_capacity) big_prims[pos] = prim;
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 4: medium triangles (slivers next to DEM outliers, coarse grids): one warp per
+    // triangle, lanes stride over the pixel centres of its bbox ----
+    const uint32_t n_med = sm.mcount;
+    for (uint32_t w = tid >> 5; w < n_med; w += VF_GEOM_THREADS / 32) {
+        const uint32_t e = sm.mqueue[w];                   // (queue slot << 1) | k
+        const uint32_t q = sm.queue[e >> 1], k = e & 1u;
+        const uint32_t qj = q / VF_GEOM_TX, qi = q - qj * VF_GEOM_TX;
+        const uint32_t prim = 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
+        const uint32_t ai = k ? qi + 1 : qi, aj = qj, bi = qi, bj = qj + 1, ci = qi + 1, cj = k ? qj + 1 : qj;
+        VfSubTri t;
+        t.v[0].X = sm.xy[aj][ai].x; t.v[0].Y = sm.xy[aj][ai].y; t.v[0].zn = sm.zn[aj][ai];
+        t.v[1].X = sm.xy[bj][bi].x; t.v[1].Y = sm.xy[bj][bi].y; t.v[1].zn = sm.zn[bj][bi];
+        t.v[2].X = sm.xy[cj][ci].x; t.v[2].Y = sm.xy[cj][ci].y; t.v[2].zn = sm.zn[cj][ci];
+        int x0, x1, y0, y1;
+        vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
+        vf_warp_raster(t, x0, x1, y0, y1, lane, [&](int px, int py, const int64_t ed[3]) {
+            float zf = 0.0f;
+            if (depth) {
+                float b[3];
+                vf_barycentric(ed, b);
+                zf = vf_depth_at(t, b);
+                if (!(zf < 1.0f)) return;
+            }
+            vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
+        });
     }
 }
 
 // ---------------------------------------------------------------------------------------
-// exclusive prefix sum of tile_count[0..n) -> tile_off[0..n]; zeroes tile_cursor. One CTA.
+// k_bin: one thread per queued primitive (large bbox or needs clipping).  Rebuilds the
+// primitive, takes the union pixel bbox of its front-facing sub-triangles and appends one
+// (tile, prim) pair per overlapped tile; positions come from a warp prefix sum + one atomic.
+__global__ void __launch_bounds__(256)
+k_bin(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+      const uint32_t* __restrict__ big_prims, uint32_t big_capacity,
+      uint32_t* __restrict__ tile_count, uint32_t* __restrict__ pair_tile,
+      uint32_t* __restrict__ pair_prim, uint32_t* __restrict__ counters, uint32_t capacity) {
+    const uint32_t n = min(counters[VF_CNT_BIG], big_capacity);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u;            // whole warps stay in the loop together
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n_round; p += stride) {
+        int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+        uint32_t prim = 0;
+        bool live = false;
+        if (p < n) {
+            prim = big_prims[p];
+            VfVtx tri[3];
+            vf_prim_vertices(f, axis, dem, prim, tri);
+            int bx0 = 1 << 30, bx1 = -1, by0 = 1 << 30, by1 = -1;
+            const bool clipped = vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
+                int x0, x1, y0, y1;
+                if (vf_area2(t) >= 0) return;
+                if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
+                bx0 = min(bx0, x0); bx1 = max(bx1, x1);
+                by0 = min(by0, y0); by1 = max(by1, y1);
+            });
+            if (clipped) atomicAdd(&counters[VF_CNT_CLIPPED], 1u);
+            if (bx1 >= bx0 && by1 >= by0) {
+                live = true;
+                tx0 = bx0 / VF_TILE; tx1 = bx1 / VF_TILE;
+                ty0 = by0 / VF_TILE; ty1 = by1 / VF_TILE;
+            }
+        }
+        const uint32_t nt = live ? (uint32_t)((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) : 0u;
+        if (__ballot_sync(0xffffffffu, nt != 0u) == 0u) continue;
+        uint32_t incl = nt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= (uint32_t)d) incl += t;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(&counters[VF_CNT_PAIRS], total);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        uint32_t pos = base + incl - nt;
+        for (int ty = ty0; ty <= ty1; ++ty)
+            for (int tx = tx0; tx <= tx1; ++tx, ++pos) {
+                if (pos < capacity) {
+                    const uint32_t tile = (uint32_t)ty * f.tiles_x + (uint32_t)tx;
+                    pair_tile[pos] = tile;
+                    pair_prim[pos] = prim;
+                    atomicAdd(&tile_count[tile], 1u);
+                }
+            }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// exclusive prefix sum of tile_count[0..n) -> tile_off[0..n]; zeroes tile_cursor.  One CTA.
+// Also records the high-water marks (pairs, queued primitives) used for overflow detection.
 __global__ void __launch_bounds__(1024)
 k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
        uint32_t* __restrict__ tile_cursor, uint32_t n, const uint32_t* __restrict__ counters,
-       uint32_t* __restrict__ max_pairs) {
+       uint32_t* __restrict__ high_water) {
     __shared__ uint32_t warp_sum[32];
     __shared__ uint32_t carry;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
-    if (tid == 0) carry = 0;
+    if (tid == 0) {
+        carry = 0;
+        atomicMax(&high_water[0], counters[VF_CNT_PAIRS]);
+        atomicMax(&high_water[1], counters[VF_CNT_BIG]);
+    }
     __syncthreads();
+    if (counters[VF_CNT_PAIRS] == 0u) {                    // nothing binned: all offsets are zero
+        for (uint32_t idx = tid; idx <= n; idx += 1024) tile_off[idx] = 0u;
+        return;
+    }
     for (uint32_t base = 0; base < n; base += 1024) {
         const uint32_t idx = base + tid;
         const uint32_t v = idx < n ? tile_count[idx] : 0u;
@@ -202,7 +391,7 @@ k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
                 const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
                 if (lane >= (uint32_t)d) w += t;
             }
-            warp_sum[lane] = w;          // inclusive over warps
+            warp_sum[lane] = w;
         }
         __syncthreads();
         const uint32_t prev_warps = wid ? warp_sum[wid - 1] : 0u;
@@ -215,10 +404,7 @@ k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
         if (tid == 1023) carry = c + prev_warps + incl;
         __syncthreads();
     }
-    if (tid == 0) {
-        tile_off[n] = carry;
-        atomicMax(max_pairs, counters[VF_CNT_PAIRS]);   // high-water mark over a batch
-    }
+    if (tid == 0) tile_off[n] = carry;
 }
 
 __global__ void k_scatter(const uint32_t* __restrict__ pair_tile, const uint32_t* __restrict__ pair_prim,
@@ -235,18 +421,20 @@ __global__ void k_scatter(const uint32_t* __restrict__ pair_tile, const uint32_t
 
 // ---------------------------------------------------------------------------------------
 // k_raster: one CTA per 16x16 screen tile, 256 threads.
-//   coverage phase: thread k takes the k-th primitive of the tile's list, rebuilds its
-//   screen-space triangle(s) with the same arithmetic as k_geom and resolves visibility in
-//   shared memory -- atomicMax(prim+1) (no depth: last drawn wins, src/terrain/pipeline.rs:133)
-//   or atomicMin((depth<<32)|prim) (depth Less).
-//   shading phase: thread = pixel; rebuilds the winning primitive, perspective-correct
-//   varyings, fragment stage, exact sRGB8; 4 pixels are packed per 16-byte store.
+//   merge   : the tile's slice of the visibility buffer (written by k_geom's micro path) is
+//             loaded into shared memory and the buffer is reset for the next frame;
+//   coverage: thread k takes the k-th binned primitive of the tile, rebuilds its screen-space
+//             triangle(s) with the same arithmetic as k_bin and resolves in shared memory --
+//             atomicMax(prim+1) (no depth: last drawn wins, src/terrain/pipeline.rs:133) or
+//             atomicMin((depth<<32)|prim) (depth Less);
+//   shading : thread = pixel; rebuilds the winning primitive, perspective-correct varyings,
+//             fragment stage, exact sRGB8; 4 pixels are packed per 16-byte store.
 __global__ void __launch_bounds__(256)
 k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
          const float* __restrict__ dem, const float4* __restrict__ lut,
-         const float* __restrict__ thr_g, const uint32_t* __restrict__ tile_off,
-         const uint32_t* __restrict__ sorted_prim, uint32_t clear_rgba,
-         uint8_t* __restrict__ out_rgba, uint32_t* __restrict__ out_vis) {
+         const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,
+         const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ sorted_prim,
+         uint32_t clear_rgba, uint8_t* __restrict__ out_rgba, uint32_t* __restrict__ out_vis) {
     __shared__ unsigned long long s_key[VF_TILE * VF_TILE];
     __shared__ float s_thr[256];
     const uint32_t tid = threadIdx.x;
@@ -255,48 +443,57 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
     const uint32_t beg = tile_off[tile], end = tile_off[tile + 1];
     const bool depth = f.depth != 0;
-
-    s_thr[tid] = thr_g[tid];
-    s_key[tid] = depth ? ~0ull : 0ull;
-    __syncthreads();
-
-    for (uint32_t k = beg + tid; k < end; k += 256) {
-        const uint32_t prim = sorted_prim[k];
-        VfVtx tri[3];
-        vf_prim_vertices(f, axis, dem, prim, tri);
-        vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
-            if (vf_area2(t) >= 0) return;
-            int x0, x1, y0, y1;
-            if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
-            x0 = max(x0, px0); x1 = min(x1, px0 + VF_TILE - 1);
-            y0 = max(y0, py0); y1 = min(y1, py0 + VF_TILE - 1);
-            for (int py = y0; py <= y1; ++py)
-                for (int px = x0; px <= x1; ++px) {
-                    int64_t e[3];
-                    if (!vf_covers(t, px, py, e)) continue;
-                    const int idx = (py - py0) * VF_TILE + (px - px0);
-                    if (depth) {
-                        float b[3];
-                        vf_barycentric(e, b);
-                        const float zf = vf_depth_at(t, b);
-                        if (!(zf < 1.0f)) continue;
-                        atomicMin(&s_key[idx], ((unsigned long long)__float_as_uint(zf) << 32) | prim);
-                    } else {
-                        atomicMax(&s_key[idx], (unsigned long long)(prim + 1u));
-                    }
-                }
-        });
-    }
-    __syncthreads();
-
+    const unsigned long long empty = depth ? ~0ull : 0ull;
     const int lx = (int)(tid & 15u), ly = (int)(tid >> 4);
     const int px = px0 + lx, py = py0 + ly;
-    const unsigned long long key = s_key[tid];
+    const bool inb = px < (int)f.W && py < (int)f.H;
+
+    s_thr[tid] = thr_g[tid];
+    unsigned long long key = empty;
+    if (inb) {
+        unsigned long long* g = vis + (size_t)py * f.W + px;
+        key = *g;
+        if (!depth) key &= 0xffffffffull;
+        if (key != empty) *g = empty;                       // self-cleaning: ready for the next frame
+    }
+    if (beg != end) {                                       // block-uniform
+        s_key[tid] = key;
+        __syncthreads();
+        for (uint32_t k = beg + tid; k < end; k += 256) {
+            const uint32_t prim = sorted_prim[k];
+            VfVtx tri[3];
+            vf_prim_vertices(f, axis, dem, prim, tri);
+            vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
+                if (vf_area2(t) >= 0) return;
+                int x0, x1, y0, y1;
+                if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
+                x0 = max(x0, px0); x1 = min(x1, px0 + VF_TILE - 1);
+                y0 = max(y0, py0); y1 = min(y1, py0 + VF_TILE - 1);
+                for (int qy = y0; qy <= y1; ++qy)
+                    for (int qx = x0; qx <= x1; ++qx) {
+                        int64_t e[3];
+                        if (!vf_covers(t, qx, qy, e)) continue;
+                        float zf = 0.0f;
+                        if (depth) {
+                            float b[3];
+                            vf_barycentric(e, b);
+                            zf = vf_depth_at(t, b);
+                            if (!(zf < 1.0f)) continue;
+                        }
+                        vf_vis_update(&s_key[(qy - py0) * VF_TILE + (qx - px0)], depth, prim, zf);
+                    }
+            });
+        }
+        __syncthreads();
+        key = s_key[tid];
+    } else {
+        __syncthreads();                                    // s_thr
+    }
+
     uint32_t id1;
     if (depth) id1 = key == ~0ull ? 0u : (uint32_t)(key & 0xffffffffull) + 1u;
     else id1 = (uint32_t)key;
     uint32_t rgba = clear_rgba;
-    const bool inb = px < (int)f.W && py < (int)f.H;
     if (id1 != 0u && inb) {
         VfVtx tri[3];
         vf_prim_vertices(f, axis, dem, id1 - 1u, tri);
@@ -321,7 +518,7 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     }
     if (out_vis && inb) out_vis[(size_t)py * f.W + px] = id1;
 
-    // 4 horizontally adjacent pixels -> one 16-byte store (rows are 16 px = 64 B per tile)
+    // 4 horizontally adjacent pixels -> one 16-byte store (a tile row is 64 contiguous bytes)
     const uint32_t r1 = __shfl_down_sync(0xffffffffu, rgba, 1);
     const uint32_t r2 = __shfl_down_sync(0xffffffffu, rgba, 2);
     const uint32_t r3 = __shfl_down_sync(0xffffffffu, rgba, 3);

@@ -258,8 +258,8 @@ def main():
             "mpix_per_s": fps * W * H / 1e6,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},
-            "gpu_launches": args.steps * F * 4,
-            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom", "ms_bin": "k_scan+k_scatter", "ms_raster": "k_raster"}[dom],
+            "gpu_launches": args.steps * F * 5,   # k_geom, k_bin, k_scan, k_scatter, k_raster per frame
+            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom", "ms_bin": "k_bin+k_scan+k_scatter", "ms_raster": "k_raster"}[dom],
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                          "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kmed[dom],
                          "frame": {"algorithmic_bytes": ALGO_BYTES_FRAME, "ms": kmed["ms_total"], "achieved": frame_achieved, "frac": frame_achieved / peak},

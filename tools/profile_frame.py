@@ -11,8 +11,10 @@ sc = vf.Scene(1920, 1080, grid=4096, colormap="terrain")
 sc.set_height_from_r32f(synthetic_dem(0, 4096))
 if mode == "northstar":
     sc.set_shading("northstar", depth=False); sc.set_sun(35.0, 120.0); sc.set_exposure(1.1); sc.set_auto_height_range()
+sc.render_batch_device(vf.orbit_cameras(32)[:2])   # warm-up (module load, buffers)
 ms = sc.render_batch_device(vf.orbit_cameras(32)[:n])
 print("frames", n, "ms", round(ms, 3), "ms/frame", round(ms / n, 4))
 sc.enable_timing(True)
-sc.render_batch_device(vf.orbit_cameras(32)[:1])
-print({k: (round(v, 4) if isinstance(v, float) else v) for k, v in sc.render_metrics().items()})
+for k in (0, 5, 11):
+    sc.render_batch_device(vf.orbit_cameras(32)[k:k + 1])
+    print(k, {a: (round(v, 4) if isinstance(v, float) else v) for a, v in sc.render_metrics().items()})

@@ -17,6 +17,7 @@ k_triangle(uint32_t W, uint32_t H, const float* __restrict__ thr_g, uint8_t* __r
     const float pos[3][2] = {{-0.8f, -0.8f}, {0.8f, -0.8f}, {0.0f, 0.8f}};
     const float col[3][3] = {{1.0f, 0.2f, 0.2f}, {0.2f, 1.0f, 0.2f}, {0.2f, 0.2f, 1.0f}};
     VfFrame f;
+    f.sparse = 0;
     f.hw = __fmul_rn(0.5f, (float)W); f.hh = __fmul_rn(0.5f, (float)H);
     VfSubTri t;
 #pragma unroll

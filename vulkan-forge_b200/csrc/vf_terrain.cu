@@ -264,6 +264,9 @@ static void build_frame(const vf_scene* s, const float* u, VfFrame* f) {
     f->Wd = s->Wd; f->Hd = s->Hd; f->dem_pitch = s->pitch;
     f->tiles_x = s->tiles_x; f->tiles_y = s->tiles_y;
     f->mode = s->mode; f->depth = s->depth;
+    const float* P = f->P; const float* V = f->V;
+    f->sparse = (P[1] == 0 && P[2] == 0 && P[3] == 0 && P[4] == 0 && P[6] == 0 && P[7] == 0 && P[8] == 0 &&
+                 P[9] == 0 && P[12] == 0 && P[13] == 0 && V[3] == 0 && V[7] == 0 && V[11] == 0 && V[15] == 1.0f) ? 1 : 0;
 }
 
 static uint32_t clear_rgba8() {

@@ -70,7 +70,7 @@ __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool de
 // centres of the bbox.  Large bboxes (needles next to DEM outliers: hundreds of pixels long, a
 // fraction of a pixel wide): lanes take the scanlines of the longer bbox axis, bound the
 // covered interval on each with a conservative float evaluation of the three edge functions
-// (margin 2/256 px; the numerators are exact int64) and run the exact integer coverage test only
+// (margin 4/256 px) and run the exact integer coverage test only
 // on the pixel centres inside it.  Coverage decisions are always the exact test's.
 template <typename Emit>
 __device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1, int y0, int y1,
@@ -88,31 +88,36 @@ __device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1
     const bool rows = bh >= bw;                      // scanlines along the longer axis
     const int m0 = rows ? y0 : x0, m1 = rows ? y1 : x1;      // major range (pixels)
     const int n0 = rows ? x0 : y0, n1 = rows ? x1 : y1;      // minor range (pixels)
-    // per edge: e = cu * (minor - ou) + ck * (major - ok)
-    float cu[3], ou[3];
-    int32_t ck[3], ok[3];
+    // per edge: e = cu * (minor - ou) + ck * (major - ok); the zero crossing along the minor axis is
+    // minor = ou - ck * (major - ok) / cu.  Evaluated in float (|ck|, |major - ok| < 2^25, so each
+    // factor rounds by <= 2^-24 relative): absolute error < 3 sub-pixel units wherever the crossing
+    // lies inside the guard band; the +-4 margin below keeps the interval conservative.
+    float rcu[3], ou[3], ckf[3], okf[3];
+    bool lower[3], used[3];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         const VfSVtx& a = t.v[(i + 1) % 3];
         const VfSVtx& b = t.v[(i + 2) % 3];
         const int32_t A = b.Y - a.Y, B = -(b.X - a.X);
-        cu[i] = (float)(rows ? A : B);
-        ck[i] = rows ? B : A;
+        const int32_t cu = rows ? A : B;
+        used[i] = cu != 0;
+        lower[i] = cu > 0;
+        rcu[i] = used[i] ? __frcp_rn((float)cu) : 0.0f;
+        ckf[i] = (float)(rows ? B : A);
         ou[i] = (float)(rows ? a.X : a.Y);
-        ok[i] = rows ? a.Y : a.X;
+        okf[i] = (float)(rows ? a.Y : a.X);
     }
+    const float n_lo = (float)(n0 * VF_SUBPIX + VF_HALFPIX), n_hi = (float)(n1 * VF_SUBPIX + VF_HALFPIX);
     for (int mj = m0 + (int)lane; mj <= m1; mj += 32) {
-        const int32_t sm = mj * VF_SUBPIX + VF_HALFPIX;
-        float lo = (float)(n0 * VF_SUBPIX + VF_HALFPIX), hi = (float)(n1 * VF_SUBPIX + VF_HALFPIX);
+        const float smf = (float)(mj * VF_SUBPIX + VF_HALFPIX);
+        float lo = n_lo, hi = n_hi;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-            if (cu[i] != 0.0f) {
-                const float v = ou[i] - (float)((int64_t)ck[i] * (int64_t)(sm - ok[i])) / cu[i];
-                if (cu[i] > 0.0f) lo = fmaxf(lo, v); else hi = fminf(hi, v);
-            }
+            const float v = fmaf(-(ckf[i] * (smf - okf[i])), rcu[i], ou[i]);
+            if (used[i]) { if (lower[i]) lo = fmaxf(lo, v); else hi = fminf(hi, v); }
         }
-        int c0 = (int)ceilf((lo - (float)(VF_HALFPIX + 2)) * (1.0f / VF_SUBPIX));
-        int c1 = (int)floorf((hi - (float)(VF_HALFPIX - 2)) * (1.0f / VF_SUBPIX));
+        int c0 = (int)ceilf((lo - (float)(VF_HALFPIX + 4)) * (1.0f / VF_SUBPIX));
+        int c1 = (int)floorf((hi - (float)(VF_HALFPIX - 4)) * (1.0f / VF_SUBPIX));
         c0 = max(c0, n0); c1 = min(c1, n1);
         for (int c = c0; c <= c1; ++c) {
             const int px = rows ? c : mj, py = rows ? mj : c;

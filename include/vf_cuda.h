@@ -56,6 +56,7 @@ typedef struct {
     uint32_t clipped_prims;  /* primitives that took the Sutherland-Hodgman path */
     uint32_t tiles;          /* screen tiles (16x16 px) */
     uint32_t big_prims;      /* primitives routed to the binned path (large or clipped) */
+    uint32_t tma;            /* 1 if the DEM tiles were staged with TMA (grid == DEM, identity mapping) */
     float ms_geom, ms_bin, ms_raster, ms_total; /* CUDA-event times, only when timing enabled */
 } vf_frame_stats_t;
 

@@ -254,3 +254,23 @@ def test_renderer_draws_stored_terrain(vf, oracle, luts, synthetic_dem):
     assert np.array_equal(a, ref)
     r.set_sun(35.0, 300.0)                                             # flipping the sun changes the shading
     assert not np.array_equal(a, r.render_rgba())
+
+
+def test_tma_staging_matches_gather_path(ext, synthetic_dem, monkeypatch):
+    """grid == DEM with identity texel mapping -> DEM tiles staged by TMA (cp.async.bulk.tensor);
+    VF_DISABLE_TMA forces the __ldg gather path.  Both must give the same bytes."""
+    dem = synthetic_dem(11, 512)
+    frames = {}
+    for disable in (False, True):
+        if disable:
+            monkeypatch.setenv("VF_DISABLE_TMA", "1")
+        sc = ext.Scene(640, 360, grid=512, colormap="terrain")
+        sc.set_height_from_r32f(dem)
+        sc.set_shading("northstar", depth=True)
+        frames[disable] = sc.render_rgba()
+        assert sc.render_metrics()["tma"] == (0 if disable else 1)
+    assert np.array_equal(frames[False], frames[True])
+    sc = ext.Scene(64, 64, grid=100, colormap="terrain")        # grid != DEM: gather path
+    sc.set_height_from_r32f(dem)
+    sc.render_rgba()
+    assert sc.render_metrics()["tma"] == 0

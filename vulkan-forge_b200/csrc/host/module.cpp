@@ -306,7 +306,7 @@ public:
         check(vf_scene_last_stats(scene_, &st));
         py::dict d;
         d["bin_pairs"] = st.bin_pairs; d["bin_capacity"] = st.bin_capacity;
-        d["clipped_prims"] = st.clipped_prims; d["tiles"] = st.tiles; d["big_prims"] = st.big_prims;
+        d["clipped_prims"] = st.clipped_prims; d["tiles"] = st.tiles; d["big_prims"] = st.big_prims; d["tma"] = st.tma;
         d["ms_geom"] = st.ms_geom; d["ms_bin"] = st.ms_bin; d["ms_raster"] = st.ms_raster; d["ms_total"] = st.ms_total;
         return d;
     }

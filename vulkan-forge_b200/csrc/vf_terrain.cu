@@ -2,6 +2,7 @@
 // replaces: Scene / TerrainSpike GPU state + draw + readback, src/scene/mod.rs:60-335,
 // src/terrain/mod.rs:258-493, src/terrain/pipeline.rs:19-143.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -9,6 +10,21 @@
 
 #include "vf_internal.h"
 #include "vf_terrain_kernels.cuh"
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
+typedef CUresult (*vf_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                      const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                      CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static vf_tmap_encode_fn tmap_encoder() {
+    static vf_tmap_encode_fn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult st;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &st) != cudaSuccess ||
+            st != cudaDriverEntryPointSuccess) { (void)cudaGetLastError(); p = nullptr; }
+        return (vf_tmap_encode_fn)p;
+    }();
+    return fn;
+}
 
 struct vf_scene {
     int W = 0, H = 0;
@@ -32,6 +48,9 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
+    alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats)
+    bool use_tma = false;                // grid == DEM with identity texel mapping
+    uint32_t* d_flag = nullptr;
     uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
     uint32_t* d_pair_tile = nullptr; uint32_t* d_pair_prim = nullptr; uint32_t* d_sorted = nullptr;
     uint32_t capacity = 0;
@@ -51,7 +70,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_dem); cudaFree(s->d_axis); cudaFree(s->d_lut); cudaFree(s->d_frame);
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
-    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big);
+    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -125,6 +144,29 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
                               cudaMemcpyHostToDevice, s->stream));
     int rc = scene_rebuild_axis(s);
     if (rc) return rc;
+    // TMA path: every grid index must fetch the texel of the same index (f32 rounding of
+    // u*W can break this near the upper end at large sizes), checked on the device
+    s->use_tma = false;
+    memset(&s->dem_map, 0, sizeof s->dem_map);
+    if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
+        if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
+        const uint32_t one = 1u;
+        uint32_t flag = 0u;
+        VF_CUDA(cudaMemcpyAsync(s->d_flag, &one, 4, cudaMemcpyHostToDevice, s->stream));
+        k_axis_identity<<<(s->G + 255) / 256, 256, 0, s->stream>>>(s->d_axis, s->G, s->d_flag);
+        VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
+        VF_CUDA(cudaStreamSynchronize(s->stream));
+        if (flag == 1u) {
+            const cuuint64_t gdim[2] = {w, h};
+            const cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4};
+            const cuuint32_t box[2] = {VF_TMA_BOX_X, VF_TMA_BOX_Y};
+            const cuuint32_t estr[2] = {1, 1};
+            const CUresult cr = tmap_encoder()(&s->dem_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box, estr,
+                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            s->use_tma = cr == CUDA_SUCCESS;
+        }
+    }
     VF_CUDA(cudaStreamSynchronize(s->stream));
     return VF_OK;
 }
@@ -290,8 +332,12 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         s->visbuf_depth = f.depth;
     }
     const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
-    k_geom<<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
-        f, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
+    if (s->use_tma)
+        k_geom<true><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
+            f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
+    else
+        k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
+            f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
     k_bin<<<148 * 2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_big, s->big_capacity, s->d_tile_count,
                                           s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);
@@ -318,6 +364,7 @@ static int scene_finish_stats(vf_scene* s) {
     s->stats.bin_pairs = s->h_counters[VF_CNT_PAIRS];
     s->stats.clipped_prims = s->h_counters[VF_CNT_CLIPPED];
     s->stats.bin_capacity = s->capacity;
+    s->stats.tma = s->use_tma ? 1u : 0u;
     s->stats.big_prims = s->h_counters[VF_CNT_BIG];
     s->stats.tiles = s->n_tiles;
     if (s->timing) {

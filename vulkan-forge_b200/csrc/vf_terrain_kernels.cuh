@@ -14,7 +14,33 @@
 // src/terrain/pipeline.rs:107-140.  Results are independent of scheduling: visibility is a max
 // over primitive ids (no depth) or a min over (depth, id) keys (depth), both order-free.
 #pragma once
+#include <cuda.h>          // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
 #include "vf_device.cuh"
+
+// ---- TMA / mbarrier primitives (sm_90+; SASS: UTMALDG / SYNCS) ----------------------------
+__device__ __forceinline__ uint32_t vf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void vf_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(vf_smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void vf_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(vf_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void vf_tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(vf_smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(vf_smem_u32(bar)) : "memory");
+}
+// bounded wait: a mis-encoded tensor map must fault the launch, not hang the GPU
+__device__ __forceinline__ void vf_mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(vf_smem_u32(bar)), "r"(parity) : "memory");
+        if (spin > (1u << 24)) __trap();
+    }
+}
+#define VF_TMA_BOX_X 36      // 33 texels + padding to a 16-byte multiple (144 B rows)
+#define VF_TMA_BOX_Y 33
 
 struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid index
 
@@ -40,6 +66,12 @@ __global__ void k_axis(VfAxis* __restrict__ axis, uint32_t G, float step, float 
     a.tx = vf_texel_index(a.uv, Wd);
     a.ty = vf_texel_index(a.uv, Hd);
     axis[i] = a;
+}
+
+// flag[0] stays 1 only if every grid index maps to the texel of the same index (tx[i]==i, ty[i]==i)
+__global__ void k_axis_identity(const VfAxis* __restrict__ axis, uint32_t G, uint32_t* __restrict__ flag) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < G && (axis[i].tx != (int)i || axis[i].ty != (int)i)) atomicAnd(flag, 0u);
 }
 
 __device__ __forceinline__ void vf_grid_vertex(const VfFrame& f, const VfAxis* __restrict__ axis,
@@ -129,6 +161,9 @@ __device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1
 
 // ---------------------------------------------------------------------------------------
 struct VfGeomSmem {
+    alignas(128) float dem[VF_TMA_BOX_Y][VF_TMA_BOX_X];   // TMA destination (DEM tile of this CTA)
+    VfAxis ax[VF_GEOM_VX], az[VF_GEOM_VY];    // axis entries of the tile's columns / rows
+    alignas(8) uint64_t mbar;
     int2 xy[VF_GEOM_VY][VF_GEOM_VX];          // snapped screen position (valid when fl & 64)
     float zn[VF_GEOM_VY][VF_GEOM_VX];         // z/w
     uint8_t fl[VF_GEOM_VY][VF_GEOM_VX + 3];   // clip flags
@@ -137,14 +172,31 @@ struct VfGeomSmem {
     uint32_t qcount, mcount;
 };
 
+// TMA = true: grid == DEM and the nearest-texel mapping is the identity (checked on the host side
+// by k_axis_identity), so the CTA's 33x33 texels are one 2-D box: a single cp.async.bulk.tensor
+// (UTMALDG) stages them in shared memory while the threads stage the axis entries.  Otherwise the
+// texels are gathered through the axis tables with coalesced __ldg row loads.
+template <bool TMA>
 __global__ void __launch_bounds__(VF_GEOM_THREADS, 4)
-k_geom(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
-       const float* __restrict__ dem, unsigned long long* __restrict__ vis,
-       uint32_t* __restrict__ big_prims, uint32_t big_capacity, uint32_t* __restrict__ counters) {
+k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap dem_map,
+       const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+       unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims, uint32_t big_capacity,
+       uint32_t* __restrict__ counters) {
     __shared__ VfGeomSmem sm;
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t i0 = blockIdx.x * VF_GEOM_TX, j0 = blockIdx.y * VF_GEOM_TY;
-    if (tid == 0) { sm.qcount = 0u; sm.mcount = 0u; }
+    if (tid == 0) {
+        sm.qcount = 0u; sm.mcount = 0u;
+        if (TMA) {
+            vf_mbar_init(&sm.mbar, 1u);
+            vf_mbar_expect_tx(&sm.mbar, VF_TMA_BOX_X * VF_TMA_BOX_Y * 4u);
+            vf_tma_load_2d(&sm.dem[0][0], &dem_map, (int)i0, (int)j0, &sm.mbar);   // OOB texels read 0
+        }
+    }
+    if (tid < VF_GEOM_VX) sm.ax[tid] = axis[min(i0 + tid, f.G - 1u)];
+    else if (tid >= 64u && tid < 64u + VF_GEOM_VY) sm.az[tid - 64u] = axis[min(j0 + tid - 64u, f.G - 1u)];
+    __syncthreads();
+    if (TMA) vf_mbar_wait(&sm.mbar, 0u);
 
     // ---- phase 1: every vertex of the 33x33 block once ----
     for (uint32_t v = tid; v < VF_GEOM_VX * VF_GEOM_VY; v += VF_GEOM_THREADS) {
@@ -155,7 +207,9 @@ k_geom(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
         uint32_t fl = 63u;
         if (i < f.G && j < f.G) {
             VfVtx o;
-            vf_grid_vertex(f, axis, dem, i, j, o);
+            const VfAxis ax = sm.ax[li], az = sm.az[lj];
+            const float h_tex = TMA ? sm.dem[lj][li] : __ldg(dem + (size_t)az.ty * f.dem_pitch + ax.tx);
+            vf_vertex_stage(f, ax.coord, az.coord, ax.uv, az.uv, h_tex, o);
             fl = vf_clip_flags(o.c);
             if (fl & 64u) {
                 VfSVtx s;

@@ -80,6 +80,15 @@ def orbit_uniform_blocks(vf, scene, n, frames):
     return scene.camera_blocks(vf.orbit_cameras(n)[:frames])
 
 
+def host_threads():
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1, which must not
+    throttle the CPU arm)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def cpu_reference_fps(frames_budget_s, dem, uniforms, hmin, hmax, min_frames=2, max_frames=64):
     """Reference CPU path stand-in (oracle, all host threads) on a bounded sample of the workload."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -90,10 +99,10 @@ def cpu_reference_fps(frames_budget_s, dem, uniforms, hmin, hmax, min_frames=2, 
     n = 0
     while n < max_frames and (n < min_frames or time.perf_counter() - t0 < frames_budget_s):
         oracle.render_terrain(W, H, G, dem, uniforms[n % len(uniforms)], lut, mode=oracle.MODE_NORTHSTAR, depth=False,
-                              h_min=hmin, h_max=hmax)
+                              h_min=hmin, h_max=hmax, threads=host_threads())
         n += 1
     dt = time.perf_counter() - t0
-    return n / dt, n, oracle.max_threads(), dt
+    return n / dt, n, host_threads(), dt
 
 
 def run_reference(args):
@@ -116,7 +125,7 @@ def run_reference(args):
     def step(k):
         for j in range(per_step):
             oracle.render_terrain(W, H, G, dem, us[(k * per_step + j) % len(us)], lut, mode=oracle.MODE_NORTHSTAR,
-                                  h_min=hmin, h_max=hmax)
+                                  h_min=hmin, h_max=hmax, threads=host_threads())
     for k in range(args.warmup):
         step(k)
     t0 = time.perf_counter()
@@ -130,7 +139,7 @@ def run_reference(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "c3: Scene 1920x1080, DEM 4096^2 seed 0, grid 4096, terrain LUT, NORTHSTAR", "frames_per_step": per_step},
         "mpix_per_s": fps * W * H / 1e6,
-        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": oracle.max_threads(), "kind": "port",
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": host_threads(), "kind": "port",
                          "sample": f"{args.steps}x{per_step} frames of the same workload; oracle/ (C + OpenMP); the reference's wgpu software path is unavailable on this box"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -141,7 +150,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--frames", type=int, default=8, help="frames per step per GPU")
@@ -244,7 +253,7 @@ def main():
         achieved = dom_bytes / (kmed[dom] * 1e-3) / 1e9
         frame_achieved = ALGO_BYTES_FRAME / (kmed["ms_total"] * 1e-3) / 1e9
         cpu = None
-        if world == 1 or rank == 0:
+        if world == 1:                                     # reported at N=1 only
             us = [np.asarray(blocks[i]) for i in range(min(F, 4))]
             cfps, cn, cores, cdt = cpu_reference_fps(args.cpu_seconds, dem, us, float(hmin), float(hmax))
             cpu = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": "port",

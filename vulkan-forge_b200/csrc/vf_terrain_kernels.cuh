@@ -50,6 +50,7 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_GEOM_VX (VF_GEOM_TX + 1)
 #define VF_GEOM_VY (VF_GEOM_TY + 1)
 #define VF_MICRO_MAX 4         // pixel-centre count up to which one thread rasterises a triangle
+#define VF_THIN_MAX 4          // bbox extent (pixels) along the minor axis up to which one thread walks the runs
 #define VF_MEDIUM_MAX 4096     // ... up to which one warp does (lanes stride over the bbox); larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
@@ -98,22 +99,21 @@ __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool de
 }
 
 // ---------------------------------------------------------------------------------------
-// Warp-cooperative rasterisation of one triangle.  Small bboxes: lanes stride over the pixel
-// centres of the bbox.  Large bboxes (needles next to DEM outliers: hundreds of pixels long, a
-// fraction of a pixel wide): lanes take the scanlines of the longer bbox axis, bound the
-// covered interval on each with a conservative float evaluation of the three edge functions
-// (margin 4/256 px) and run the exact integer coverage test only
-// on the pixel centres inside it.  Coverage decisions are always the exact test's.
+// Warp-cooperative rasterisation of one triangle (edges set up at the bbox origin (x0, y0)).
+// Small bboxes: lanes stride over the pixel centres of the bbox.  Large bboxes: lanes take the
+// scanlines of the longer bbox axis, bound the covered interval on each with a conservative float
+// evaluation of the three edge functions (margin 4/256 px) and run the exact integer coverage
+// test only on the pixel centres inside it.  Coverage decisions are always the exact test's.
+// emit(px, py, e) receives the BIASED edge values (vf_edges_unbias restores them).
 template <typename Emit>
-__device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1, int y0, int y1,
+__device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, const VfEdges& s, int x0, int x1, int y0, int y1,
                                                uint32_t lane, Emit&& emit) {
     const uint32_t bw = (uint32_t)(x1 - x0 + 1), bh = (uint32_t)(y1 - y0 + 1), npx = bw * bh;
     if (npx <= 64u) {
         for (uint32_t idx = lane; idx < npx; idx += 32u) {
-            const uint32_t ry = idx / bw;
-            const int px = x0 + (int)(idx - ry * bw), py = y0 + (int)ry;
+            const uint32_t ry = idx / bw, rx = idx - ry * bw;
             int64_t ed[3];
-            if (vf_covers(t, px, py, ed)) emit(px, py, ed);
+            if (vf_edges_at(s, (int)rx, (int)ry, ed)) emit(x0 + (int)rx, y0 + (int)ry, ed);
         }
         return;
     }
@@ -129,13 +129,11 @@ __device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
         const VfSVtx& a = t.v[(i + 1) % 3];
-        const VfSVtx& b = t.v[(i + 2) % 3];
-        const int32_t A = b.Y - a.Y, B = -(b.X - a.X);
-        const int32_t cu = rows ? A : B;
+        const int32_t cu = rows ? s.A[i] : s.B[i];
         used[i] = cu != 0;
         lower[i] = cu > 0;
         rcu[i] = used[i] ? __frcp_rn((float)cu) : 0.0f;
-        ckf[i] = (float)(rows ? B : A);
+        ckf[i] = (float)(rows ? s.B[i] : s.A[i]);
         ou[i] = (float)(rows ? a.X : a.Y);
         okf[i] = (float)(rows ? a.Y : a.X);
     }
@@ -154,7 +152,49 @@ __device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, int x0, int x1
         for (int c = c0; c <= c1; ++c) {
             const int px = rows ? c : mj, py = rows ? mj : c;
             int64_t ed[3];
-            if (vf_covers(t, px, py, ed)) emit(px, py, ed);
+            if (vf_edges_at(s, px - x0, py - y0, ed)) emit(px, py, ed);
+        }
+    }
+}
+
+// Thread-serial rasterisation of a THIN triangle (bbox at most VF_THIN_MAX pixels across its
+// minor axis): the needles next to DEM outliers are a fraction of a pixel wide and hundreds of
+// pixels long, so the work must follow the covered samples, not the bbox.  For every line of the
+// minor axis the covered run along the major axis is bounded in float (crossing of each edge,
+// margin 1/64 px: the float error is < 2^-8 px for crossings inside the bbox) and the exact test
+// decides every sample of the run.
+template <typename Emit>
+__device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1, int y0, int y1, Emit&& emit) {
+    const bool cols = (x1 - x0) <= (y1 - y0);        // minor axis = x: walk columns, runs along y
+    const int nmin = cols ? x1 - x0 + 1 : y1 - y0 + 1;
+    const int nmaj = cols ? y1 - y0 + 1 : x1 - x0 + 1;
+    int32_t amaj[3];
+    float rmaj[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        amaj[i] = cols ? s.B[i] : s.A[i];
+        rmaj[i] = amaj[i] != 0 ? __fdividef(-1.0f, (float)amaj[i] * (float)VF_SUBPIX) : 0.0f;
+    }
+    for (int m = 0; m < nmin; ++m) {
+        int64_t base[3];
+        float lo = 0.0f, hi = (float)(nmaj - 1);
+        bool dead = false;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            base[i] = s.E[i] + (int64_t)(cols ? s.A[i] : s.B[i]) * (int64_t)(m * VF_SUBPIX);
+            const float tc = (float)base[i] * rmaj[i];           // base + amaj*256*t = 0
+            if (amaj[i] > 0) lo = fmaxf(lo, tc);
+            else if (amaj[i] < 0) hi = fminf(hi, tc);
+            else dead = dead || base[i] < 0;
+        }
+        if (dead) continue;
+        int c0 = (int)ceilf(lo - 0.015625f), c1 = (int)floorf(hi + 0.015625f);
+        c0 = max(c0, 0); c1 = min(c1, nmaj - 1);
+        for (int c = c0; c <= c1; ++c) {
+            int64_t ed[3];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) ed[i] = base[i] + (int64_t)amaj[i] * (int64_t)(c * VF_SUBPIX);
+            if ((ed[0] | ed[1] | ed[2]) >= 0) emit(cols ? x0 + m : x0 + c, cols ? y0 + c : y0 + m, ed);
         }
     }
 }
@@ -169,7 +209,8 @@ struct VfGeomSmem {
     uint8_t fl[VF_GEOM_VY][VF_GEOM_VX + 3];   // clip flags
     uint16_t queue[VF_GEOM_TX * VF_GEOM_TY];  // cells that survived the quad-level cull
     uint16_t mqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // triangles for the warp-cooperative rasteriser
-    uint32_t qcount, mcount;
+    uint16_t nqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // thin triangles (needles) for the thread-serial rasteriser
+    uint32_t qcount, mcount, ncount;
 };
 
 // TMA = true: grid == DEM and the nearest-texel mapping is the identity (checked on the host side
@@ -186,7 +227,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t i0 = blockIdx.x * VF_GEOM_TX, j0 = blockIdx.y * VF_GEOM_TY;
     if (tid == 0) {
-        sm.qcount = 0u; sm.mcount = 0u;
+        sm.qcount = 0u; sm.mcount = 0u; sm.ncount = 0u;
         if (TMA) {
             vf_mbar_init(&sm.mbar, 1u);
             vf_mbar_expect_tx(&sm.mbar, VF_TMA_BOX_X * VF_TMA_BOX_Y * 4u);
@@ -258,96 +299,115 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
     // ---- phase 3: surviving triangles, densely packed over the CTA ----
     const uint32_t n_entries = 2u * sm.qcount;
     const bool depth = f.depth != 0;
+    // triangle k of the queued cell `slot`: T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
+    auto load_tri = [&](uint32_t slot, uint32_t k, VfSubTri& t) -> uint32_t {
+        const uint32_t q = sm.queue[slot];
+        const uint32_t qj = q / VF_GEOM_TX, qi = q - qj * VF_GEOM_TX;
+        const uint32_t ai = k ? qi + 1 : qi, aj = qj, bi = qi, bj = qj + 1, ci = qi + 1, cj = k ? qj + 1 : qj;
+        t.v[0].X = sm.xy[aj][ai].x; t.v[0].Y = sm.xy[aj][ai].y; t.v[0].zn = sm.zn[aj][ai];
+        t.v[1].X = sm.xy[bj][bi].x; t.v[1].Y = sm.xy[bj][bi].y; t.v[1].zn = sm.zn[bj][bi];
+        t.v[2].X = sm.xy[cj][ci].x; t.v[2].Y = sm.xy[cj][ci].y; t.v[2].zn = sm.zn[cj][ci];
+        return 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
+    };
+    auto emit_sample = [&](const VfSubTri& t, const VfEdges& es, uint32_t prim, int px, int py, int64_t ed[3]) {
+        float zf = 0.0f;
+        if (depth) {
+            float b[3];
+            vf_edges_unbias(es, ed);
+            vf_barycentric(ed, b);
+            zf = vf_depth_at(t, b);
+            if (!(zf < 1.0f)) return;
+        }
+        vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
+    };
     for (uint32_t base = 0; base < n_entries; base += VF_GEOM_THREADS) {
         const uint32_t e = base + tid;
-        bool to_big = false, to_med = false;
+        bool to_big = false, to_med = false, to_thin = false;
         uint32_t prim = 0;
         if (e < n_entries) {
             const uint32_t q = sm.queue[e >> 1], k = e & 1u;
             const uint32_t qj = q / VF_GEOM_TX, qi = q - qj * VF_GEOM_TX;
-            prim = 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
-            // T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
-            const uint32_t ai = k ? qi + 1 : qi, aj = qj;          // v0
-            const uint32_t bi = qi, bj = qj + 1;                   // v1 = c
-            const uint32_t ci = qi + 1, cj = k ? qj + 1 : qj;      // v2
+            const uint32_t ai = k ? qi + 1 : qi, aj = qj, bi = qi, bj = qj + 1, ci = qi + 1, cj = k ? qj + 1 : qj;
             const uint32_t f0 = sm.fl[aj][ai], f1 = sm.fl[bj][bi], f2 = sm.fl[cj][ci];
             if (!(f0 & f1 & f2 & 63u)) {
                 if (!(f0 & f1 & f2 & 64u)) {
+                    prim = 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
                     to_big = true;                                  // needs clipping
                 } else {
                     VfSubTri t;
-                    t.v[0].X = sm.xy[aj][ai].x; t.v[0].Y = sm.xy[aj][ai].y; t.v[0].zn = sm.zn[aj][ai];
-                    t.v[1].X = sm.xy[bj][bi].x; t.v[1].Y = sm.xy[bj][bi].y; t.v[1].zn = sm.zn[bj][bi];
-                    t.v[2].X = sm.xy[cj][ci].x; t.v[2].Y = sm.xy[cj][ci].y; t.v[2].zn = sm.zn[cj][ci];
+                    prim = load_tri(e >> 1, k, t);
                     int x0, x1, y0, y1;
                     if (vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1) && vf_area2(t) < 0) {
-                        const int npx = (x1 - x0 + 1) * (y1 - y0 + 1);
-                        if (npx > VF_MEDIUM_MAX) {
-                            to_big = true;
-                        } else if (npx > VF_MICRO_MAX) {
+                        const int bw = x1 - x0 + 1, bh = y1 - y0 + 1, npx = bw * bh;
+                        if (npx <= VF_MICRO_MAX) {
+                            VfEdges es;
+                            vf_edges_setup(t, x0, y0, es);
+                            for (int dy = 0; dy < bh; ++dy)
+                                for (int dx = 0; dx < bw; ++dx) {
+                                    int64_t ed[3];
+                                    if (vf_edges_at(es, dx, dy, ed)) emit_sample(t, es, prim, x0 + dx, y0 + dy, ed);
+                                }
+                        } else if (min(bw, bh) <= VF_THIN_MAX) {
+                            to_thin = true;
+                        } else if (npx <= VF_MEDIUM_MAX) {
                             to_med = true;
                         } else {
-                            for (int py = y0; py <= y1; ++py)
-                                for (int px = x0; px <= x1; ++px) {
-                                    int64_t ed[3];
-                                    if (!vf_covers(t, px, py, ed)) continue;
-                                    float zf = 0.0f;
-                                    if (depth) {
-                                        float b[3];
-                                        vf_barycentric(ed, b);
-                                        zf = vf_depth_at(t, b);
-                                        if (!(zf < 1.0f)) continue;
-                                    }
-                                    vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
-                                }
+                            to_big = true;
                         }
                     }
                 }
             }
+        }
+        const uint32_t below = (1u << lane) - 1u;
+        const uint32_t nm = __ballot_sync(0xffffffffu, to_thin);
+        if (nm) {
+            uint32_t nb = 0;
+            if (lane == 0) nb = atomicAdd(&sm.ncount, (uint32_t)__popc(nm));
+            nb = __shfl_sync(0xffffffffu, nb, 0);
+            if (to_thin) sm.nqueue[nb + __popc(nm & below)] = (uint16_t)e;
         }
         const uint32_t mm = __ballot_sync(0xffffffffu, to_med);
         if (mm) {
             uint32_t mb = 0;
             if (lane == 0) mb = atomicAdd(&sm.mcount, (uint32_t)__popc(mm));
             mb = __shfl_sync(0xffffffffu, mb, 0);
-            if (to_med) sm.mqueue[mb + __popc(mm & ((1u << lane) - 1u))] = (uint16_t)(((e >> 1) << 1) | (e & 1u));
+            if (to_med) sm.mqueue[mb + __popc(mm & below)] = (uint16_t)e;
         }
         const uint32_t m = __ballot_sync(0xffffffffu, to_big);
         if (m) {
             uint32_t gb = 0;
             if (lane == 0) gb = atomicAdd(&counters[VF_CNT_BIG], (uint32_t)__popc(m));
             gb = __shfl_sync(0xffffffffu, gb, 0);
-            const uint32_t pos = gb + __popc(m & ((1u << lane) - 1u));
+            const uint32_t pos = gb + __popc(m & below);
             if (to_big && pos < big_capacity) big_prims[pos] = prim;
         }
     }
     __syncthreads();
 
-    // ---- phase 4: medium triangles (slivers next to DEM outliers, coarse grids): one warp per
-    // triangle, lanes stride over the pixel centres of its bbox ----
-    const uint32_t n_med = sm.mcount;
-    for (uint32_t w = tid >> 5; w < n_med; w += VF_GEOM_THREADS / 32) {
-        const uint32_t e = sm.mqueue[w];                   // (queue slot << 1) | k
-        const uint32_t q = sm.queue[e >> 1], k = e & 1u;
-        const uint32_t qj = q / VF_GEOM_TX, qi = q - qj * VF_GEOM_TX;
-        const uint32_t prim = 2u * ((j0 + qj) * (f.G - 1u) + (i0 + qi)) + k;
-        const uint32_t ai = k ? qi + 1 : qi, aj = qj, bi = qi, bj = qj + 1, ci = qi + 1, cj = k ? qj + 1 : qj;
+    // ---- phase 4a: thin triangles (needles next to DEM outliers), one thread each, packed ----
+    const uint32_t n_thin = sm.ncount;
+    for (uint32_t w = tid; w < n_thin; w += VF_GEOM_THREADS) {
+        const uint32_t e = sm.nqueue[w];                   // (queue slot << 1) | k
         VfSubTri t;
-        t.v[0].X = sm.xy[aj][ai].x; t.v[0].Y = sm.xy[aj][ai].y; t.v[0].zn = sm.zn[aj][ai];
-        t.v[1].X = sm.xy[bj][bi].x; t.v[1].Y = sm.xy[bj][bi].y; t.v[1].zn = sm.zn[bj][bi];
-        t.v[2].X = sm.xy[cj][ci].x; t.v[2].Y = sm.xy[cj][ci].y; t.v[2].zn = sm.zn[cj][ci];
+        const uint32_t prim = load_tri(e >> 1, e & 1u, t);
         int x0, x1, y0, y1;
         vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
-        vf_warp_raster(t, x0, x1, y0, y1, lane, [&](int px, int py, const int64_t ed[3]) {
-            float zf = 0.0f;
-            if (depth) {
-                float b[3];
-                vf_barycentric(ed, b);
-                zf = vf_depth_at(t, b);
-                if (!(zf < 1.0f)) return;
-            }
-            vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
-        });
+        VfEdges es;
+        vf_edges_setup(t, x0, y0, es);
+        vf_thin_raster(es, x0, x1, y0, y1, [&](int px, int py, int64_t ed[3]) { emit_sample(t, es, prim, px, py, ed); });
+    }
+
+    // ---- phase 4b: medium triangles (coarse grids): one warp per triangle ----
+    const uint32_t n_med = sm.mcount;
+    for (uint32_t w = tid >> 5; w < n_med; w += VF_GEOM_THREADS / 32) {
+        const uint32_t e = sm.mqueue[w];
+        VfSubTri t;
+        const uint32_t prim = load_tri(e >> 1, e & 1u, t);
+        int x0, x1, y0, y1;
+        vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
+        VfEdges es;
+        vf_edges_setup(t, x0, y0, es);
+        vf_warp_raster(t, es, x0, x1, y0, y1, lane, [&](int px, int py, int64_t ed[3]) { emit_sample(t, es, prim, px, py, ed); });
     }
 }
 

@@ -50,8 +50,7 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_GEOM_VX (VF_GEOM_TX + 1)
 #define VF_GEOM_VY (VF_GEOM_TY + 1)
 #define VF_MICRO_MAX 4         // pixel-centre count up to which one thread rasterises a triangle
-#define VF_THIN_MAX 4          // bbox extent (pixels) along the minor axis up to which one thread walks the runs
-#define VF_MEDIUM_MAX 4096     // ... up to which one warp does (lanes stride over the bbox); larger -> binned
+#define VF_MEDIUM_MAX 4096     // bbox pixels up to which one thread walks the runs (queued, packed); larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
 enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_WORDS = 4 };
@@ -99,70 +98,13 @@ __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool de
 }
 
 // ---------------------------------------------------------------------------------------
-// Warp-cooperative rasterisation of one triangle (edges set up at the bbox origin (x0, y0)).
-// Small bboxes: lanes stride over the pixel centres of the bbox.  Large bboxes: lanes take the
-// scanlines of the longer bbox axis, bound the covered interval on each with a conservative float
-// evaluation of the three edge functions (margin 4/256 px) and run the exact integer coverage
-// test only on the pixel centres inside it.  Coverage decisions are always the exact test's.
+// Thread-serial rasterisation of one triangle (edges set up at the bbox origin (x0, y0)).  The
+// needles next to DEM outliers are a fraction of a pixel wide, up to hundreds of pixels long and
+// tilted, so the work must follow the covered samples, not the bbox: the thread walks the lines of
+// the SHORTER bbox axis; on each the covered run along the longer axis is bounded in float
+// (crossing of each edge, margin 1/64 px: the float error is < 2^-8 px for crossings inside the
+// bbox) and the exact test decides every sample of the run.
 // emit(px, py, e) receives the BIASED edge values (vf_edges_unbias restores them).
-template <typename Emit>
-__device__ __forceinline__ void vf_warp_raster(const VfSubTri& t, const VfEdges& s, int x0, int x1, int y0, int y1,
-                                               uint32_t lane, Emit&& emit) {
-    const uint32_t bw = (uint32_t)(x1 - x0 + 1), bh = (uint32_t)(y1 - y0 + 1), npx = bw * bh;
-    if (npx <= 64u) {
-        for (uint32_t idx = lane; idx < npx; idx += 32u) {
-            const uint32_t ry = idx / bw, rx = idx - ry * bw;
-            int64_t ed[3];
-            if (vf_edges_at(s, (int)rx, (int)ry, ed)) emit(x0 + (int)rx, y0 + (int)ry, ed);
-        }
-        return;
-    }
-    const bool rows = bh >= bw;                      // scanlines along the longer axis
-    const int m0 = rows ? y0 : x0, m1 = rows ? y1 : x1;      // major range (pixels)
-    const int n0 = rows ? x0 : y0, n1 = rows ? x1 : y1;      // minor range (pixels)
-    // per edge: e = cu * (minor - ou) + ck * (major - ok); the zero crossing along the minor axis is
-    // minor = ou - ck * (major - ok) / cu.  Evaluated in float (|ck|, |major - ok| < 2^25, so each
-    // factor rounds by <= 2^-24 relative): absolute error < 3 sub-pixel units wherever the crossing
-    // lies inside the guard band; the +-4 margin below keeps the interval conservative.
-    float rcu[3], ou[3], ckf[3], okf[3];
-    bool lower[3], used[3];
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-        const VfSVtx& a = t.v[(i + 1) % 3];
-        const int32_t cu = rows ? s.A[i] : s.B[i];
-        used[i] = cu != 0;
-        lower[i] = cu > 0;
-        rcu[i] = used[i] ? __frcp_rn((float)cu) : 0.0f;
-        ckf[i] = (float)(rows ? s.B[i] : s.A[i]);
-        ou[i] = (float)(rows ? a.X : a.Y);
-        okf[i] = (float)(rows ? a.Y : a.X);
-    }
-    const float n_lo = (float)(n0 * VF_SUBPIX + VF_HALFPIX), n_hi = (float)(n1 * VF_SUBPIX + VF_HALFPIX);
-    for (int mj = m0 + (int)lane; mj <= m1; mj += 32) {
-        const float smf = (float)(mj * VF_SUBPIX + VF_HALFPIX);
-        float lo = n_lo, hi = n_hi;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-            const float v = fmaf(-(ckf[i] * (smf - okf[i])), rcu[i], ou[i]);
-            if (used[i]) { if (lower[i]) lo = fmaxf(lo, v); else hi = fminf(hi, v); }
-        }
-        int c0 = (int)ceilf((lo - (float)(VF_HALFPIX + 4)) * (1.0f / VF_SUBPIX));
-        int c1 = (int)floorf((hi - (float)(VF_HALFPIX - 4)) * (1.0f / VF_SUBPIX));
-        c0 = max(c0, n0); c1 = min(c1, n1);
-        for (int c = c0; c <= c1; ++c) {
-            const int px = rows ? c : mj, py = rows ? mj : c;
-            int64_t ed[3];
-            if (vf_edges_at(s, px - x0, py - y0, ed)) emit(px, py, ed);
-        }
-    }
-}
-
-// Thread-serial rasterisation of a THIN triangle (bbox at most VF_THIN_MAX pixels across its
-// minor axis): the needles next to DEM outliers are a fraction of a pixel wide and hundreds of
-// pixels long, so the work must follow the covered samples, not the bbox.  For every line of the
-// minor axis the covered run along the major axis is bounded in float (crossing of each edge,
-// margin 1/64 px: the float error is < 2^-8 px for crossings inside the bbox) and the exact test
-// decides every sample of the run.
 template <typename Emit>
 __device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1, int y0, int y1, Emit&& emit) {
     const bool cols = (x1 - x0) <= (y1 - y0);        // minor axis = x: walk columns, runs along y
@@ -208,9 +150,8 @@ struct VfGeomSmem {
     float zn[VF_GEOM_VY][VF_GEOM_VX];         // z/w
     uint8_t fl[VF_GEOM_VY][VF_GEOM_VX + 3];   // clip flags
     uint16_t queue[VF_GEOM_TX * VF_GEOM_TY];  // cells that survived the quad-level cull
-    uint16_t mqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // triangles for the warp-cooperative rasteriser
-    uint16_t nqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // thin triangles (needles) for the thread-serial rasteriser
-    uint32_t qcount, mcount, ncount;
+    uint16_t nqueue[2 * VF_GEOM_TX * VF_GEOM_TY];  // non-micro triangles (needles) for the run rasteriser
+    uint32_t qcount, ncount;
 };
 
 // TMA = true: grid == DEM and the nearest-texel mapping is the identity (checked on the host side
@@ -227,7 +168,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const uint32_t i0 = blockIdx.x * VF_GEOM_TX, j0 = blockIdx.y * VF_GEOM_TY;
     if (tid == 0) {
-        sm.qcount = 0u; sm.mcount = 0u; sm.ncount = 0u;
+        sm.qcount = 0u; sm.ncount = 0u;
         if (TMA) {
             vf_mbar_init(&sm.mbar, 1u);
             vf_mbar_expect_tx(&sm.mbar, VF_TMA_BOX_X * VF_TMA_BOX_Y * 4u);
@@ -322,7 +263,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
     };
     for (uint32_t base = 0; base < n_entries; base += VF_GEOM_THREADS) {
         const uint32_t e = base + tid;
-        bool to_big = false, to_med = false, to_thin = false;
+        bool to_big = false, to_thin = false;
         uint32_t prim = 0;
         if (e < n_entries) {
             const uint32_t q = sm.queue[e >> 1], k = e & 1u;
@@ -347,10 +288,8 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
                                     int64_t ed[3];
                                     if (vf_edges_at(es, dx, dy, ed)) emit_sample(t, es, prim, x0 + dx, y0 + dy, ed);
                                 }
-                        } else if (min(bw, bh) <= VF_THIN_MAX) {
-                            to_thin = true;
                         } else if (npx <= VF_MEDIUM_MAX) {
-                            to_med = true;
+                            to_thin = true;
                         } else {
                             to_big = true;
                         }
@@ -366,13 +305,6 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
             nb = __shfl_sync(0xffffffffu, nb, 0);
             if (to_thin) sm.nqueue[nb + __popc(nm & below)] = (uint16_t)e;
         }
-        const uint32_t mm = __ballot_sync(0xffffffffu, to_med);
-        if (mm) {
-            uint32_t mb = 0;
-            if (lane == 0) mb = atomicAdd(&sm.mcount, (uint32_t)__popc(mm));
-            mb = __shfl_sync(0xffffffffu, mb, 0);
-            if (to_med) sm.mqueue[mb + __popc(mm & below)] = (uint16_t)e;
-        }
         const uint32_t m = __ballot_sync(0xffffffffu, to_big);
         if (m) {
             uint32_t gb = 0;
@@ -384,7 +316,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
     }
     __syncthreads();
 
-    // ---- phase 4a: thin triangles (needles next to DEM outliers), one thread each, packed ----
+    // ---- phase 4: non-micro triangles (needles next to DEM outliers, coarse grids), one thread each, packed ----
     const uint32_t n_thin = sm.ncount;
     for (uint32_t w = tid; w < n_thin; w += VF_GEOM_THREADS) {
         const uint32_t e = sm.nqueue[w];                   // (queue slot << 1) | k
@@ -395,19 +327,6 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
         VfEdges es;
         vf_edges_setup(t, x0, y0, es);
         vf_thin_raster(es, x0, x1, y0, y1, [&](int px, int py, int64_t ed[3]) { emit_sample(t, es, prim, px, py, ed); });
-    }
-
-    // ---- phase 4b: medium triangles (coarse grids): one warp per triangle ----
-    const uint32_t n_med = sm.mcount;
-    for (uint32_t w = tid >> 5; w < n_med; w += VF_GEOM_THREADS / 32) {
-        const uint32_t e = sm.mqueue[w];
-        VfSubTri t;
-        const uint32_t prim = load_tri(e >> 1, e & 1u, t);
-        int x0, x1, y0, y1;
-        vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
-        VfEdges es;
-        vf_edges_setup(t, x0, y0, es);
-        vf_warp_raster(t, es, x0, x1, y0, y1, lane, [&](int px, int py, int64_t ed[3]) { emit_sample(t, es, prim, px, py, ed); });
     }
 }
 

@@ -9,7 +9,7 @@
 #include <vector>
 
 #include "vf_internal.h"
-#include "vf_terrain_kernels.cuh"
+#include "vf_geom_march.cuh"
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
 typedef CUresult (*vf_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -48,7 +48,8 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
-    alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats)
+    alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
+    alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
     bool use_tma = false;                // grid == DEM with identity texel mapping
     uint32_t* d_flag = nullptr;
     uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
@@ -148,6 +149,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     // u*W can break this near the upper end at large sizes), checked on the device
     s->use_tma = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
+    memset(&s->dem_map_gm, 0, sizeof s->dem_map_gm);
     if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
         if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
         const uint32_t one = 1u;
@@ -164,7 +166,11 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
             const CUresult cr = tmap_encoder()(&s->dem_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box, estr,
                                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            s->use_tma = cr == CUDA_SUCCESS;
+            const cuuint32_t box_gm[2] = {VF_GM_BOX_X, VF_GM_VROWS};
+            const CUresult cr2 = tmap_encoder()(&s->dem_map_gm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box_gm, estr,
+                                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            s->use_tma = cr == CUDA_SUCCESS && cr2 == CUDA_SUCCESS;
         }
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
@@ -318,6 +324,37 @@ static uint32_t clear_rgba8() {
     return enc(0.02f) | (enc(0.02f) << 8) | (enc(0.03f) << 16) | 0xff000000u;
 }
 
+// k_geom_march: persistent grid of warp workers; rows per task shrink on coarse grids so that every
+// warp of the machine gets a few tasks
+static int launch_geom_march(vf_scene* s, const VfFrame& f) {
+    static int sm_count = 0;
+    static bool attr_done = false;
+    const size_t smem = VF_GM_WARPS * sizeof(VfGmWarp);
+    if (!attr_done) {
+        int dev = 0;
+        VF_CUDA(cudaGetDevice(&dev));
+        VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+    }
+    const uint32_t gm = s->G - 1;
+    const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
+    const uint32_t workers = (uint32_t)sm_count * 2u * VF_GM_WARPS;
+    uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
+    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
+    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
+    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * 2u, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
+#define VF_GM_LAUNCH(T, D) k_geom_march<T, D><<<ctas, VF_GM_WARPS * 32, smem, s->stream>>>( \
+        f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, rows)
+    if (s->use_tma) { if (f.depth) VF_GM_LAUNCH(true, true); else VF_GM_LAUNCH(true, false); }
+    else            { if (f.depth) VF_GM_LAUNCH(false, true); else VF_GM_LAUNCH(false, false); }
+#undef VF_GM_LAUNCH
+    return VF_OK;
+}
+
 // enqueue one frame into slot `slot` on s->stream
 static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vis) {
     VfFrame f;
@@ -331,13 +368,18 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaMemsetAsync(s->d_visbuf, f.depth ? 0xff : 0x00, (size_t)s->W * s->H * 8, s->stream));
         s->visbuf_depth = f.depth;
     }
-    const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
-    if (s->use_tma)
-        k_geom<true><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
-            f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
-    else
-        k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
-            f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
+    if (getenv("VF_GEOM_TILED")) {        // previous generation (CTA tiles through shared memory), kept for A/B runs
+        const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
+        if (s->use_tma)
+            k_geom<true><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
+                f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
+        else
+            k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
+                f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
+    } else {
+        int rc = launch_geom_march(s, f);
+        if (rc) return rc;
+    }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
     k_bin<<<148 * 2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_big, s->big_capacity, s->d_tile_count,
                                           s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);

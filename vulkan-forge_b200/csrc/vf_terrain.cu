@@ -334,10 +334,10 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         int dev = 0;
         VF_CUDA(cudaGetDevice(&dev));
         VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_march<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_march<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_march<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_march<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+#define VF_GM_ATTR(T, D, S) VF_CUDA(cudaFuncSetAttribute(k_geom_march<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))
+        VF_GM_ATTR(true, true, true);   VF_GM_ATTR(true, true, false);   VF_GM_ATTR(true, false, true);   VF_GM_ATTR(true, false, false);
+        VF_GM_ATTR(false, true, true);  VF_GM_ATTR(false, true, false);  VF_GM_ATTR(false, false, true);  VF_GM_ATTR(false, false, false);
+#undef VF_GM_ATTR
         attr_done = true;
     }
     const uint32_t gm = s->G - 1;
@@ -347,10 +347,12 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
     const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
     const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * 2u, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
-#define VF_GM_LAUNCH(T, D) k_geom_march<T, D><<<ctas, VF_GM_WARPS * 32, smem, s->stream>>>( \
+#define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, smem, s->stream>>>( \
         f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, rows)
-    if (s->use_tma) { if (f.depth) VF_GM_LAUNCH(true, true); else VF_GM_LAUNCH(true, false); }
-    else            { if (f.depth) VF_GM_LAUNCH(false, true); else VF_GM_LAUNCH(false, false); }
+#define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
+    if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
+    else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }
+#undef VF_GM_LAUNCH2
 #undef VF_GM_LAUNCH
     return VF_OK;
 }
@@ -368,7 +370,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaMemsetAsync(s->d_visbuf, f.depth ? 0xff : 0x00, (size_t)s->W * s->H * 8, s->stream));
         s->visbuf_depth = f.depth;
     }
-    if (getenv("VF_GEOM_TILED")) {        // previous generation (CTA tiles through shared memory), kept for A/B runs
+    if (!f.sparse || getenv("VF_GEOM_TILED")) {   // general matrices; also kept for A/B runs
         const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
         if (s->use_tma)
             k_geom<true><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(

@@ -20,6 +20,7 @@
 //              large / clipped ones go to the global queue of k_bin.
 // Results do not depend on scheduling: the visibility resolve is order-free (vf_vis_update).
 #pragma once
+#include <type_traits>
 #include "vf_terrain_kernels.cuh"
 
 #define VF_GM_WARPS 8                        // warps per CTA (each independent)
@@ -230,10 +231,15 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
     uint32_t cur = next_task();
     issue(cur, 0u);
-    // frame constants of the row loop
-    const float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
-    const float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
-    const float exag = f.exag, hw = f.hw, hh = f.hh;
+    // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
+    float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
+    float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
+    float exag = f.exag, hw = f.hw, hh = f.hh;
+#define VF_PIN(x) asm volatile("" : "+f"(x))
+    VF_PIN(V4); VF_PIN(V5); VF_PIN(V6); VF_PIN(V8); VF_PIN(V9); VF_PIN(V10);
+    VF_PIN(P0); VF_PIN(P5); VF_PIN(P10); VF_PIN(P11); VF_PIN(P14); VF_PIN(P15);
+    VF_PIN(exag); VF_PIN(hw); VF_PIN(hh);
+#undef VF_PIN
 
     while (cur < ntasks) {
         const uint32_t nxt = next_task();
@@ -259,74 +265,138 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
 
         int32_t pX = 0, pY = 0, pXn = 0, pYn = 0;          // previous row: own vertex and right neighbour
         float pZ = 0.0f, pZn = 0.0f;
-        uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state (0 = inside the guard band)
+        uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the guard band)
         const float* texel = &w.dem[stage][((strip * VF_GM_QCOLS) & 3u) + lane];
         const float* gtexel = dem + ax.tx;
-        float h_next = 0.0f;
-        if (!TMA) h_next = __ldg(gtexel + (size_t)w.ty[0] * f.dem_pitch);
         const uint32_t cell0 = (j0 - 1u) * gm + i;          // cell index of (row r-1, column i) is cell0 + r*gm
         uint32_t r = 0u;
+        auto load_h = [&](uint32_t rr) -> float {
+            return TMA ? texel[rr * VF_GM_BOX_X] : __ldg(gtexel + (size_t)w.ty[rr] * f.dem_pitch);
+        };
+        // vertex stage (terrain.wgsl:44-66), bit-identical to the sparse form of vf_vertex_stage
+        auto clip_pos = [&](uint32_t rr, float h_tex, float c[4]) {
+            const float h = SHIPPED ? __fadd_rn(h_tex, __fadd_rn(sx25, w.kz[rr])) : h_tex;
+            const float wy = __fmul_rn(h, exag), wz = w.wz[rr];
+            const float v0 = fmaf(V4, wy, fmaf(V8, wz, a0));
+            const float v1 = fmaf(V5, wy, fmaf(V9, wz, a1));
+            const float v2 = fmaf(V6, wy, fmaf(V10, wz, a2));
+            c[0] = __fmul_rn(P0, v0); c[1] = __fmul_rn(P5, v1);
+            c[2] = __fadd_rn(P14, __fmul_rn(P10, v2)); c[3] = __fadd_rn(P15, __fmul_rn(P11, v2));
+        };
+        // viewport + snap (vf_to_screen) given 1/w
+        auto snap = [&](const float c[4], float invw, int32_t& X, int32_t& Y, float& Z) {
+            const float xn = __fmul_rn(c[0], invw), yn = __fmul_rn(c[1], invw);
+            X = __float2int_rn(__fmul_rn(fmaf(xn, hw, hw), (float)VF_SUBPIX));
+            Y = __float2int_rn(__fmul_rn(fmaf(-yn, hh, hh), (float)VF_SUBPIX));
+            Z = DEPTH ? __fmul_rn(c[2], invw) : 0.0f;
+        };
+        auto append = [&](uint32_t m, bool keep, uint32_t cell, int32_t aX, int32_t aY, float aZ, int32_t bX, int32_t bY, float bZ,
+                          int32_t cX, int32_t cY, float cZ, int32_t dX, int32_t dY, float dZ) {
+            if (keep) {
+                const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
+                w.qx[0][s] = aX; w.qy[0][s] = aY;
+                w.qx[1][s] = bX; w.qy[1][s] = bY;
+                w.qx[2][s] = cX; w.qy[2][s] = cY;
+                w.qx[3][s] = dX; w.qy[3][s] = dY;
+                if (DEPTH) { w.qz[0][s] = aZ; w.qz[1][s] = bZ; w.qz[2][s] = cZ; w.qz[3][s] = dZ; }
+                w.qcell[s] = cell;
+            }
+            q.qn += (uint32_t)__popc(m);
+        };
+
+        // One vertex row, general form: tracks the clip state of the vertices; cells with a vertex
+        // outside the guard band are queued for a rebuild from scratch.
+        auto row = [&]() {
+            float c[4];
+            clip_pos(r, load_h(r), c);
+            const bool in = vf_clip_in(c) || !colv;
+            int32_t X, Y;
+            float Z;
+            snap(c, __frcp_rn(c[3]), X, Y, Z);
+            const int32_t Xn = __shfl_down_sync(0xffffffffu, X, 1), Yn = __shfl_down_sync(0xffffffffu, Y, 1);
+            float Zn = 0.0f;
+            if (DEPTH) Zn = __shfl_down_sync(0xffffffffu, Z, 1);
+            // no pixel centre inside the cell's bbox -> neither triangle draws (off-screen cells die in the drain)
+            bool keep = cellv && r > 0u &&
+                        vf_span_has_centre(min(min(pX, pXn), min(X, Xn)), max(max(pX, pXn), max(X, Xn))) &&
+                        vf_span_has_centre(min(min(pY, pYn), min(Y, Yn)), max(max(pY, pYn), max(Y, Yn)));
+            uint32_t rebuild = 0u;
+            const uint32_t nin = __ballot_sync(0xffffffffu, !in);
+            uint32_t st = 0u, stn = 0u;
+            if ((nin | pnin) != 0u) {                       // a vertex of this or the previous row is outside the guard band
+                if (nin) {
+                    st = in ? 0u : (128u | (vf_clip_flags(c) & 63u));
+                    stn = __shfl_down_sync(0xffffffffu, st, 1);
+                }
+                if (st | stn | pst | pstn) {
+                    rebuild = 0x80000000u;
+                    keep = cellv && r > 0u && !(st & stn & pst & pstn & 63u);   // not all four outside one frustum plane
+                }
+            }
+            pst = st; pstn = stn; pnin = nin;
+            const uint32_t m = __ballot_sync(0xffffffffu, keep);
+            if (m) append(m, keep, (cell0 + r * gm) | rebuild, pX, pY, pZ, pXn, pYn, pZn, X, Y, Z, Xn, Yn, Zn);
+            pX = X; pY = Y; pXn = Xn; pYn = Yn; pZ = Z; pZn = Zn;
+            ++r;
+        };
+
+        // Two vertex rows at once, straight-line (the two vertex stages interleave): taken while
+        // every vertex is inside the guard band with w in [2^-100, 2^100], where rcp.rn is
+        // MUFU.RCP + one Newton step.  Returns false (nothing consumed) when that does not hold.
+        auto row_pair = [&]() -> bool {
+            float ca[4], cb[4];
+            clip_pos(r, load_h(r), ca);
+            clip_pos(r + 1u, load_h(r + 1u), cb);
+            const float ga = __fmul_rn(VF_GUARD_K, ca[3]), gb = __fmul_rn(VF_GUARD_K, cb[3]);
+            const bool oka = (ca[3] >= 0x1p-100f) & (ca[3] <= 0x1p100f) & (ca[2] >= 0.0f) & (ca[2] <= ca[3]) &
+                             (fabsf(ca[0]) <= ga) & (fabsf(ca[1]) <= ga);
+            const bool okb = (cb[3] >= 0x1p-100f) & (cb[3] <= 0x1p100f) & (cb[2] >= 0.0f) & (cb[2] <= cb[3]) &
+                             (fabsf(cb[0]) <= gb) & (fabsf(cb[1]) <= gb);
+            if (__any_sync(0xffffffffu, colv & !(oka & okb))) return false;
+            float ra, rb;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(ca[3]));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cb[3]));
+            ra = fmaf(ra, -fmaf(ca[3], ra, -1.0f), ra);
+            rb = fmaf(rb, -fmaf(cb[3], rb, -1.0f), rb);
+            int32_t XA, YA, XB, YB;
+            float ZA, ZB;
+            snap(ca, ra, XA, YA, ZA);
+            snap(cb, rb, XB, YB, ZB);
+            const int32_t XAn = __shfl_down_sync(0xffffffffu, XA, 1), YAn = __shfl_down_sync(0xffffffffu, YA, 1);
+            const int32_t XBn = __shfl_down_sync(0xffffffffu, XB, 1), YBn = __shfl_down_sync(0xffffffffu, YB, 1);
+            float ZAn = 0.0f, ZBn = 0.0f;
+            if (DEPTH) { ZAn = __shfl_down_sync(0xffffffffu, ZA, 1); ZBn = __shfl_down_sync(0xffffffffu, ZB, 1); }
+            const int32_t eAx0 = min(XA, XAn), eAx1 = max(XA, XAn), eAy0 = min(YA, YAn), eAy1 = max(YA, YAn);   // edge of row A
+            const bool keepA = cellv &
+                vf_span_has_centre(min(min(pX, pXn), eAx0), max(max(pX, pXn), eAx1)) &
+                vf_span_has_centre(min(min(pY, pYn), eAy0), max(max(pY, pYn), eAy1));
+            const bool keepB = cellv &
+                vf_span_has_centre(min(min(XB, XBn), eAx0), max(max(XB, XBn), eAx1)) &
+                vf_span_has_centre(min(min(YB, YBn), eAy0), max(max(YB, YBn), eAy1));
+            const uint32_t mA = __ballot_sync(0xffffffffu, keepA), mB = __ballot_sync(0xffffffffu, keepB);
+            if (mA) append(mA, keepA, cell0 + r * gm, pX, pY, pZ, pXn, pYn, pZn, XA, YA, ZA, XAn, YAn, ZAn);
+            if (q.qn + (uint32_t)__popc(mB) > VF_GM_QCAP) {      // ring full (coarse grids): row B is redone after the drain
+                pX = XA; pY = YA; pXn = XAn; pYn = YAn; pZ = ZA; pZn = ZAn;
+                r += 1u;
+                return true;
+            }
+            if (mB) append(mB, keepB, cell0 + (r + 1u) * gm, XA, YA, ZA, XAn, YAn, ZAn, XB, YB, ZB, XBn, YBn, ZBn);
+            pX = XB; pY = YB; pXn = XBn; pYn = YBn; pZ = ZB; pZn = ZBn;
+            r += 2u;
+            return true;
+        };
+
+        row();                                              // row 0 primes the previous-row registers
+        bool fast = true;                                   // no vertex outside the guard band met in this task so far
         while (r < nrows) {
-#pragma unroll 2
-            for (; r < nrows && q.qn <= VF_GM_QCAP - 32u; ++r) {
-                float h_tex;
-                if (TMA) {
-                    h_tex = texel[r * VF_GM_BOX_X];
-                } else {
-                    h_tex = h_next;
-                    if (r + 1u < nrows) h_next = __ldg(gtexel + (size_t)w.ty[r + 1u] * f.dem_pitch);
-                }
-                // ---- vertex stage (terrain.wgsl:44-66), bit-identical to the sparse form of vf_vertex_stage ----
-                const float h = SHIPPED ? __fadd_rn(h_tex, __fadd_rn(sx25, w.kz[r])) : h_tex;
-                const float wy = __fmul_rn(h, exag), wz = w.wz[r];
-                const float v0 = fmaf(V4, wy, fmaf(V8, wz, a0));
-                const float v1 = fmaf(V5, wy, fmaf(V9, wz, a1));
-                const float v2 = fmaf(V6, wy, fmaf(V10, wz, a2));
-                const float c0 = __fmul_rn(P0, v0), c1 = __fmul_rn(P5, v1);
-                const float c2 = __fadd_rn(P14, __fmul_rn(P10, v2)), c3 = __fadd_rn(P15, __fmul_rn(P11, v2));
-                const float g = __fmul_rn(VF_GUARD_K, c3);
-                const bool in = (c3 > 0.0f && c2 >= 0.0f && c2 <= c3 && fabsf(c0) <= g && fabsf(c1) <= g) || !colv;
-                // ---- viewport + snap (vf_to_screen; rcp.rn == correctly rounded 1/w) ----
-                const float invw = __frcp_rn(c3);
-                const float xn = __fmul_rn(c0, invw), yn = __fmul_rn(c1, invw);
-                const int32_t X = __float2int_rn(__fmul_rn(fmaf(xn, hw, hw), (float)VF_SUBPIX));
-                const int32_t Y = __float2int_rn(__fmul_rn(fmaf(-yn, hh, hh), (float)VF_SUBPIX));
-                const float Z = DEPTH ? __fmul_rn(c2, invw) : 0.0f;
-                const int32_t Xn = __shfl_down_sync(0xffffffffu, X, 1), Yn = __shfl_down_sync(0xffffffffu, Y, 1);
-                float Zn = 0.0f;
-                if (DEPTH) Zn = __shfl_down_sync(0xffffffffu, Z, 1);
-                const uint32_t nin = __ballot_sync(0xffffffffu, !in);
-                // no pixel centre inside the cell's bbox -> neither triangle draws (off-screen cells die in the drain)
-                bool keep = cellv && r > 0u &&
-                            vf_span_has_centre(min(min(pX, pXn), min(X, Xn)), max(max(pX, pXn), max(X, Xn))) &&
-                            vf_span_has_centre(min(min(pY, pYn), min(Y, Yn)), max(max(pY, pYn), max(Y, Yn)));
-                uint32_t st = 0u, stn = 0u, rebuild = 0u;
-                if ((nin | pnin) != 0u) {                   // rare: a vertex of this or the previous row is outside the guard band
-                    if (nin) {
-                        const float c[4] = {c0, c1, c2, c3};
-                        st = in ? 0u : (128u | (vf_clip_flags(c) & 63u));
-                        stn = __shfl_down_sync(0xffffffffu, st, 1);
-                    }
-                    if (st | stn | pst | pstn) {
-                        rebuild = 0x80000000u;
-                        keep = cellv && r > 0u && !(st & stn & pst & pstn & 63u);   // not all four outside one frustum plane
-                    }
-                }
-                const uint32_t m = __ballot_sync(0xffffffffu, keep);
-                if (m) {
-                    if (keep) {
-                        const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
-                        w.qx[0][s] = pX;  w.qy[0][s] = pY;
-                        w.qx[1][s] = pXn; w.qy[1][s] = pYn;
-                        w.qx[2][s] = X;   w.qy[2][s] = Y;
-                        w.qx[3][s] = Xn;  w.qy[3][s] = Yn;
-                        if (DEPTH) { w.qz[0][s] = pZ; w.qz[1][s] = pZn; w.qz[2][s] = Z; w.qz[3][s] = Zn; }
-                        w.qcell[s] = (cell0 + r * gm) | rebuild;
-                    }
-                    q.qn += (uint32_t)__popc(m);
-                }
-                pX = X; pY = Y; pXn = Xn; pYn = Yn; pZ = Z; pZn = Zn;
-                pst = st; pstn = stn; pnin = nin;
+            if (fast) {
+#pragma unroll 1
+                while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
+                    if (!row_pair()) { fast = false; break; }
+            }
+            if (!fast || r + 1u == nrows) {
+#pragma unroll 1
+                while (r < nrows && q.qn <= VF_GM_QCAP - 32u) row();
             }
             __syncwarp();
             if (q.qn >= 16u)

@@ -33,20 +33,27 @@
 #define VF_GM_NCAP 64                        // long-triangle ring: drained in groups of 32
 #define VF_CNT_TASK 3                        // counters[] slot of the task dispenser
 
-struct VfGmWarp {
+template <bool DEPTH>
+struct VfGmWarpT {
     alignas(128) float dem[2][VF_GM_STAGE_FLOATS];       // TMA ring: texels of the current / next task (rows of 36)
     alignas(8) uint64_t mbar[2];
     float wz[VF_GM_VROWS], kz[VF_GM_VROWS];              // per row: z*spacing, 0.25*cos(1.1 z)
     int ty[VF_GM_VROWS];                                 // per row: texel row
     int32_t qx[4][VF_GM_QCAP], qy[4][VF_GM_QCAP];        // queued cells: snapped a, b, c, d
-    float qz[4][VF_GM_QCAP];
+    float qz[DEPTH ? 4 : 1][DEPTH ? VF_GM_QCAP : 1];     // depth only
     uint32_t qcell[VF_GM_QCAP];                          // cell index | bit 31: rebuild from scratch (clip flags mixed)
     int32_t nx[3][VF_GM_NCAP], ny[3][VF_GM_NCAP];        // queued long triangles
-    float nz[3][VF_GM_NCAP];
+    float nz[DEPTH ? 3 : 1][DEPTH ? VF_GM_NCAP : 1];     // depth only
     uint32_t nprim[VF_GM_NCAP];
 };
 
-struct VfGmQueues { uint32_t qhead, qn, nhead, nn; };    // ring state, warp-uniform registers
+// ring state, warp-uniform registers; crosses the call to vf_gm_drain_cells packed in one word so
+// that it never lives in local memory
+struct VfGmQueues {
+    uint32_t qhead, qn, nhead, nn;
+    __device__ __forceinline__ uint32_t pack() const { return qhead | (qn << 8) | (nhead << 16) | (nn << 24); }
+    __device__ __forceinline__ void unpack(uint32_t v) { qhead = v & 255u; qn = (v >> 8) & 255u; nhead = (v >> 16) & 255u; nn = v >> 24; }
+};
 
 // Full per-triangle treatment of a cell whose vertices are not all inside the guard band: the
 // vertex stage is redone from the grid (same code as k_bin / k_raster).  0: nothing to draw,
@@ -80,7 +87,7 @@ __device__ __forceinline__ void vf_gm_emit(const VfFrame& f, unsigned long long*
 
 // drain groups of 32 long triangles (whatever is left when `all`)
 template <bool DEPTH>
-__device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarp& w, VfGmQueues& q, bool all, uint32_t lane,
+__device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEPTH>& w, VfGmQueues& q, bool all, uint32_t lane,
                                                  unsigned long long* __restrict__ vis) {
     while (q.nn >= 32u || (all && q.nn > 0u)) {
         const uint32_t take = min(q.nn, 32u);
@@ -106,12 +113,14 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarp& w, 
 
 // drain the warp's cell ring 16 cells (two triangles each) at a time; the remainder too when `all`
 template <bool DEPTH>
-__device__ __noinline__ void vf_gm_drain_cells(const VfFrame& f, VfGmWarp& w, VfGmQueues& q, bool all,
+__device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<DEPTH>& w, uint32_t qpacked, bool all,
                                                const VfAxis* __restrict__ axis, const float* __restrict__ dem,
                                                unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims,
                                                uint32_t big_capacity, uint32_t* __restrict__ counters) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t below = (1u << lane) - 1u;
+    VfGmQueues q;
+    q.unpack(qpacked);
     while (q.qn >= 16u || (all && q.qn > 0u)) {
         const uint32_t take = min(q.qn, 16u);
         bool to_big = false, to_long = false;
@@ -123,7 +132,10 @@ __device__ __noinline__ void vf_gm_drain_cells(const VfFrame& f, VfGmWarp& w, Vf
             prim = 2u * (cell & 0x7fffffffu) + k;
             int st = 1;
             if (cell >> 31) {
-                st = vf_gm_rebuild(f, axis, dem, prim, t);
+                VfSubTri tr;                             // address escapes into the call: lives on the stack
+                st = vf_gm_rebuild(f, axis, dem, prim, tr);
+#pragma unroll
+                for (int v = 0; v < 3; ++v) { t.v[v].X = tr.v[v].X; t.v[v].Y = tr.v[v].Y; t.v[v].zn = tr.v[v].zn; }
             } else {                                     // T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
                 const uint32_t i0 = k, i2 = 1u + 2u * k;
                 t.v[0].X = w.qx[i0][slot]; t.v[0].Y = w.qy[i0][slot];
@@ -179,6 +191,7 @@ __device__ __noinline__ void vf_gm_drain_cells(const VfFrame& f, VfGmWarp& w, Vf
         __syncwarp();
         vf_gm_drain_long<DEPTH>(f, w, q, false, lane, vis);
     }
+    return q.pack();
 }
 
 // true when some pixel centre (sub-pixel 128 mod 256) lies in [mn, mx]: floor((mx-128)/256) differs
@@ -200,18 +213,16 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
              uint32_t* __restrict__ counters, uint32_t rows) {
     extern __shared__ __align__(128) unsigned char vf_gm_smem[];
     const uint32_t lane = threadIdx.x & 31u;
-    VfGmWarp& w = reinterpret_cast<VfGmWarp*>(vf_gm_smem)[threadIdx.x >> 5];
+    VfGmWarpT<DEPTH>& w = reinterpret_cast<VfGmWarpT<DEPTH>*>(vf_gm_smem)[threadIdx.x >> 5];
     const uint32_t gm = f.G - 1u;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1u) / VF_GM_QCOLS;
     const uint32_t nsegs = (gm + rows - 1u) / rows;          // rows (<= VF_GM_ROWS) cell rows per task
     const uint32_t ntasks = nstrips * nsegs;
     const uint32_t below = (1u << lane) - 1u;
 
-    auto next_task = [&]() -> uint32_t {
-        uint32_t t = 0;
-        if (lane == 0) t = atomicAdd(&counters[VF_CNT_TASK], 1u);
-        return __shfl_sync(0xffffffffu, t, 0);
-    };
+    // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
+    auto ask_task = [&]() -> uint32_t { return lane == 0 ? atomicAdd(&counters[VF_CNT_TASK], 1u) : 0u; };
+    auto got_task = [&](uint32_t t) -> uint32_t { return __shfl_sync(0xffffffffu, t, 0); };
     auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
         if (TMA && lane == 0 && task < ntasks) {
             const uint32_t strip = task % nstrips, seg = task / nstrips;
@@ -221,7 +232,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     };
     if (TMA) {                                              // thread 0 initialises every warp's pair of barriers
         if (threadIdx.x == 0) {
-            VfGmWarp* ws = reinterpret_cast<VfGmWarp*>(vf_gm_smem);
+            VfGmWarpT<DEPTH>* ws = reinterpret_cast<VfGmWarpT<DEPTH>*>(vf_gm_smem);
 #pragma unroll
             for (int k = 0; k < VF_GM_WARPS; ++k) { vf_mbar_init(&ws[k].mbar[0], 1u); vf_mbar_init(&ws[k].mbar[1], 1u); }
         }
@@ -229,8 +240,9 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     }
     VfGmQueues q = {0u, 0u, 0u, 0u};
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
-    uint32_t cur = next_task();
+    uint32_t cur = got_task(ask_task());
     issue(cur, 0u);
+    uint32_t nxt = got_task(ask_task());
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
     float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
@@ -242,8 +254,8 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
 #undef VF_PIN
 
     while (cur < ntasks) {
-        const uint32_t nxt = next_task();
         issue(nxt, stage ^ 1u);
+        const uint32_t asked = ask_task();                  // becomes `nxt` at the end of this task
         const uint32_t strip = cur % nstrips, seg = cur / nstrips;
         const uint32_t i = strip * VF_GM_QCOLS + lane, j0 = seg * rows;
         const uint32_t nrows = min(rows + 1u, f.G - j0);    // vertex rows of this task
@@ -400,12 +412,13 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             }
             __syncwarp();
             if (q.qn >= 16u)
-                vf_gm_drain_cells<DEPTH>(f, w, q, false, axis, dem, vis, big_prims, big_capacity, counters);
+                q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), false, axis, dem, vis, big_prims, big_capacity, counters));
         }
         __syncwarp();                                       // all reads of this stage and of the row tables are done
         cur = nxt;
+        nxt = got_task(asked);
         stage ^= 1u;
     }
-    vf_gm_drain_cells<DEPTH>(f, w, q, true, axis, dem, vis, big_prims, big_capacity, counters);
+    q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), true, axis, dem, vis, big_prims, big_capacity, counters));
     vf_gm_drain_long<DEPTH>(f, w, q, true, lane, vis);
 }

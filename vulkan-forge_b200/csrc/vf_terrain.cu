@@ -329,12 +329,12 @@ static uint32_t clear_rgba8() {
 static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     static int sm_count = 0;
     static bool attr_done = false;
-    const size_t smem = VF_GM_WARPS * sizeof(VfGmWarp);
+    const size_t smem_d = VF_GM_WARPS * sizeof(VfGmWarpT<true>), smem_n = VF_GM_WARPS * sizeof(VfGmWarpT<false>);
     if (!attr_done) {
         int dev = 0;
         VF_CUDA(cudaGetDevice(&dev));
         VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-#define VF_GM_ATTR(T, D, S) VF_CUDA(cudaFuncSetAttribute(k_geom_march<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem))
+#define VF_GM_ATTR(T, D, S) VF_CUDA(cudaFuncSetAttribute(k_geom_march<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((D) ? smem_d : smem_n)))
         VF_GM_ATTR(true, true, true);   VF_GM_ATTR(true, true, false);   VF_GM_ATTR(true, false, true);   VF_GM_ATTR(true, false, false);
         VF_GM_ATTR(false, true, true);  VF_GM_ATTR(false, true, false);  VF_GM_ATTR(false, false, true);  VF_GM_ATTR(false, false, false);
 #undef VF_GM_ATTR
@@ -342,12 +342,13 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     }
     const uint32_t gm = s->G - 1;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
-    const uint32_t workers = (uint32_t)sm_count * 2u * VF_GM_WARPS;
+    const uint32_t per_sm = 2u;             // CTAs per SM (launch bounds of k_geom_march)
+    const uint32_t workers = (uint32_t)sm_count * per_sm * VF_GM_WARPS;
     uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
     rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
     const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
-    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * 2u, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
-#define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, smem, s->stream>>>( \
+    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * per_sm, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
+#define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
         f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, rows)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }

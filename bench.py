@@ -45,7 +45,7 @@ class ClockSampler:
     def __init__(self, index):
         self.p = None
         try:
-            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except Exception:
             pass
@@ -74,6 +74,14 @@ class ClockSampler:
                     reasons.add(n)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (None if absent)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "dram_traffic.json"))).get(kernel)
+    except Exception:
+        return None
 
 
 def orbit_uniform_blocks(vf, scene, n, frames):
@@ -268,8 +276,9 @@ def main():
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},
             "gpu_launches": args.steps * F * 5,   # k_geom, k_bin, k_scan, k_scatter, k_raster per frame
-            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom", "ms_bin": "k_bin+k_scan+k_scatter", "ms_raster": "k_raster"}[dom],
-                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_bin+k_scan+k_scatter", "ms_raster": "k_raster"}[dom],
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": ncu_traffic({"ms_geom": "k_geom", "ms_bin": "k_bin", "ms_raster": "k_raster"}[dom]),
                          "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kmed[dom],
                          "frame": {"algorithmic_bytes": ALGO_BYTES_FRAME, "ms": kmed["ms_total"], "achieved": frame_achieved, "frac": frame_achieved / peak},
                          "kernels_ms": kmed},

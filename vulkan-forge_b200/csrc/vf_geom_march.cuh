@@ -31,7 +31,6 @@
 #define VF_GM_VROWS (VF_GM_ROWS + 1)
 #define VF_GM_QCAP 64                        // cell ring: a row adds <= 31, rows run while <= 32 wait
 #define VF_GM_NCAP 64                        // long-triangle ring: drained in groups of 32
-#define VF_CNT_TASK 3                        // counters[] slot of the task dispenser
 
 template <bool DEPTH>
 struct VfGmWarpT {

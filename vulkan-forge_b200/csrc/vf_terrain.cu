@@ -384,24 +384,33 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
-    k_bin<<<148 * 2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_big, s->big_capacity, s->d_tile_count,
-                                          s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity);
-    k_scan<<<1, 1024, 0, s->stream>>>(s->d_tile_count, s->d_tile_off, s->d_tile_cursor, s->n_tiles,
-                                      s->d_counters, s->d_maxpairs);
-    k_scatter<<<148 * 4, 256, 0, s->stream>>>(s->d_pair_tile, s->d_pair_prim, s->d_counters, s->capacity,
-                                              s->d_tile_off, s->d_tile_cursor, s->d_sorted);
+    {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
+        static int binsort_ctas = 0;
+        if (!binsort_ctas) {
+            int dev = 0, sms = 0, per_sm = 0;
+            VF_CUDA(cudaGetDevice(&dev));
+            VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_binsort, 256, 0));
+            binsort_ctas = sms * std::min(std::max(per_sm, 1), 2);
+        }
+        uint32_t big_capacity = s->big_capacity, capacity = s->capacity;
+        void* args[] = {&f, &s->d_axis, &s->d_dem, &s->d_big, &big_capacity, &s->d_tile_count, &s->d_tile_off,
+                        &s->d_tile_cursor, &s->d_pair_tile, &s->d_pair_prim, &s->d_sorted, &s->d_counters, &capacity,
+                        &s->d_maxpairs};
+        VF_CUDA(cudaLaunchCooperativeKernel((const void*)k_binsort, dim3(binsort_ctas), dim3(256), args, 0, s->stream));
+    }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
     k_raster<<<s->n_tiles, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
-                                                s->d_sorted, clear, frame, d_vis);
+                                                s->d_sorted, s->d_counters, clear, frame, d_vis);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());
     return VF_OK;
 }
 
-// h_counters layout: [0..3] last frame's counters, [4] high-water mark of requested pairs
+// h_counters layout: [0..VF_CNT_WORDS) last frame's counters, then the high-water marks (pairs, queued prims)
 static int scene_fetch_counters(vf_scene* s) {
     VF_CUDA(cudaMemcpyAsync(s->h_counters, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
-    VF_CUDA(cudaMemcpyAsync(s->h_counters + 4, s->d_maxpairs, 8, cudaMemcpyDeviceToHost, s->stream));
+    VF_CUDA(cudaMemcpyAsync(s->h_counters + VF_CNT_WORDS, s->d_maxpairs, 8, cudaMemcpyDeviceToHost, s->stream));
     return VF_OK;
 }
 
@@ -448,7 +457,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         if (rc) return rc;
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
-        const uint32_t need = s->h_counters[4], need_big = s->h_counters[5];
+        const uint32_t need = s->h_counters[VF_CNT_WORDS], need_big = s->h_counters[VF_CNT_WORDS + 1];
         if (need <= s->capacity && need_big <= s->big_capacity) return scene_finish_stats(s);
         // an overflowed frame left stale keys in the visibility buffer only if k_raster did not run
         // to completion; it always does, so the buffer is clean and the call can simply be repeated

@@ -53,7 +53,7 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_MEDIUM_MAX 4096     // bbox pixels up to which one thread walks the runs (queued, packed); larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
-enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_WORDS = 4 };
+enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_WORDS = 8 };
 
 // ---------------------------------------------------------------------------------------
 __global__ void k_axis(VfAxis* __restrict__ axis, uint32_t G, float step, float gm1,
@@ -334,11 +334,11 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
 // k_bin: one thread per queued primitive (large bbox or needs clipping).  Rebuilds the
 // primitive, takes the union pixel bbox of its front-facing sub-triangles and appends one
 // (tile, prim) pair per overlapped tile; positions come from a warp prefix sum + one atomic.
-__global__ void __launch_bounds__(256)
-k_bin(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
-      const uint32_t* __restrict__ big_prims, uint32_t big_capacity,
-      uint32_t* __restrict__ tile_count, uint32_t* __restrict__ pair_tile,
-      uint32_t* __restrict__ pair_prim, uint32_t* __restrict__ counters, uint32_t capacity) {
+__device__ __forceinline__ void
+vf_bin_phase(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+             const uint32_t* __restrict__ big_prims, uint32_t big_capacity,
+             uint32_t* __restrict__ tile_count, uint32_t* __restrict__ pair_tile,
+             uint32_t* __restrict__ pair_prim, uint32_t* __restrict__ counters, uint32_t capacity) {
     const uint32_t n = min(counters[VF_CNT_BIG], big_capacity);
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -392,26 +392,28 @@ k_bin(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, const 
 }
 
 // ---------------------------------------------------------------------------------------
-// exclusive prefix sum of tile_count[0..n) -> tile_off[0..n]; zeroes tile_cursor.  One CTA.
-// Also records the high-water marks (pairs, queued primitives) used for overflow detection.
-__global__ void __launch_bounds__(1024)
-k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
-       uint32_t* __restrict__ tile_cursor, uint32_t n, const uint32_t* __restrict__ counters,
-       uint32_t* __restrict__ high_water) {
+// exclusive prefix sum of tile_count[0..n) -> tile_off[0..n]; zeroes tile_cursor.  One CTA of
+// NT threads.  Also records the high-water marks (pairs, queued primitives) used for overflow
+// detection.
+template <uint32_t NT>
+__device__ __forceinline__ void
+vf_scan_phase(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
+              uint32_t* __restrict__ tile_cursor, uint32_t n, const uint32_t* __restrict__ counters,
+              uint32_t* __restrict__ high_water) {
     __shared__ uint32_t warp_sum[32];
     __shared__ uint32_t carry;
     const uint32_t tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
     if (tid == 0) {
         carry = 0;
-        atomicMax(&high_water[0], counters[VF_CNT_PAIRS]);
-        atomicMax(&high_water[1], counters[VF_CNT_BIG]);
+        atomicMax(&high_water[0], __ldcg(&counters[VF_CNT_PAIRS]));
+        atomicMax(&high_water[1], __ldcg(&counters[VF_CNT_BIG]));
     }
     __syncthreads();
-    if (counters[VF_CNT_PAIRS] == 0u) {                    // nothing binned: all offsets are zero
-        for (uint32_t idx = tid; idx <= n; idx += 1024) tile_off[idx] = 0u;
+    if (__ldcg(&counters[VF_CNT_PAIRS]) == 0u) {                    // nothing binned: all offsets are zero
+        for (uint32_t idx = tid; idx <= n; idx += NT) tile_off[idx] = 0u;
         return;
     }
-    for (uint32_t base = 0; base < n; base += 1024) {
+    for (uint32_t base = 0; base < n; base += NT) {
         const uint32_t idx = base + tid;
         const uint32_t v = idx < n ? tile_count[idx] : 0u;
         uint32_t incl = v;
@@ -423,7 +425,7 @@ k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
         if (lane == 31) warp_sum[wid] = incl;
         __syncthreads();
         if (wid == 0) {
-            uint32_t w = warp_sum[lane];
+            uint32_t w = lane < NT / 32u ? warp_sum[lane] : 0u;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const uint32_t t = __shfl_up_sync(0xffffffffu, w, d);
@@ -439,22 +441,53 @@ k_scan(const uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off,
             tile_cursor[idx] = 0u;
         }
         __syncthreads();
-        if (tid == 1023) carry = c + prev_warps + incl;
+        if (tid == NT - 1u) carry = c + prev_warps + incl;
         __syncthreads();
     }
     if (tid == 0) tile_off[n] = carry;
 }
 
-__global__ void k_scatter(const uint32_t* __restrict__ pair_tile, const uint32_t* __restrict__ pair_prim,
-                          const uint32_t* __restrict__ counters, uint32_t capacity,
-                          const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ tile_cursor,
-                          uint32_t* __restrict__ sorted_prim) {
-    const uint32_t n = min(counters[VF_CNT_PAIRS], capacity);
+__device__ __forceinline__ void
+vf_scatter_phase(const uint32_t* __restrict__ pair_tile, const uint32_t* __restrict__ pair_prim,
+                 const uint32_t* __restrict__ counters, uint32_t capacity,
+                 const uint32_t* __restrict__ tile_off, uint32_t* __restrict__ tile_cursor,
+                 uint32_t* __restrict__ sorted_prim) {
+    const uint32_t n = min(__ldcg(&counters[VF_CNT_PAIRS]), capacity);
     for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < n; p += gridDim.x * blockDim.x) {
         const uint32_t tile = pair_tile[p];
         const uint32_t slot = atomicAdd(&tile_cursor[tile], 1u);
         sorted_prim[tile_off[tile] + slot] = pair_prim[p];
     }
+}
+
+// ---------------------------------------------------------------------------------------
+// k_binsort: the sort-middle stage for the queued (large / clipped) primitives as ONE launch:
+// bin -> grid barrier -> per-tile prefix sum (CTA 0) -> grid barrier -> scatter.  The grid is
+// launched cooperatively (every CTA resident), the barrier is a monotonic counter in counters[].
+// With an empty queue (fine grids seen whole) the three phases are a few loads each.
+__device__ __forceinline__ void vf_grid_barrier(uint32_t* bar, uint32_t target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(bar, 1u);
+        while (*reinterpret_cast<volatile uint32_t*>(bar) < target) __nanosleep(32);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+k_binsort(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+          const uint32_t* __restrict__ big_prims, uint32_t big_capacity,
+          uint32_t* __restrict__ tile_count, uint32_t* __restrict__ tile_off, uint32_t* __restrict__ tile_cursor,
+          uint32_t* __restrict__ pair_tile, uint32_t* __restrict__ pair_prim, uint32_t* __restrict__ sorted_prim,
+          uint32_t* __restrict__ counters, uint32_t capacity, uint32_t* __restrict__ high_water) {
+    if (__ldcg(&counters[VF_CNT_BIG]) == 0u) return;     // empty queue (same answer in every CTA): k_raster sees no pairs
+    vf_bin_phase(f, axis, dem, big_prims, big_capacity, tile_count, pair_tile, pair_prim, counters, capacity);
+    vf_grid_barrier(&counters[VF_CNT_GRIDBAR], gridDim.x);
+    if (blockIdx.x == 0) vf_scan_phase<256>(tile_count, tile_off, tile_cursor, f.tiles_x * f.tiles_y, counters, high_water);
+    vf_grid_barrier(&counters[VF_CNT_GRIDBAR], 2u * gridDim.x);
+    vf_scatter_phase(pair_tile, pair_prim, counters, capacity, tile_off, tile_cursor, sorted_prim);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -472,14 +505,16 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
          const float* __restrict__ dem, const float4* __restrict__ lut,
          const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,
          const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ sorted_prim,
-         uint32_t clear_rgba, uint8_t* __restrict__ out_rgba, uint32_t* __restrict__ out_vis) {
+         const uint32_t* __restrict__ counters, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba,
+         uint32_t* __restrict__ out_vis) {
     __shared__ unsigned long long s_key[VF_TILE * VF_TILE];
     __shared__ float s_thr[256];
     const uint32_t tid = threadIdx.x;
     const uint32_t tile = blockIdx.x;
     const uint32_t tyi = tile / f.tiles_x, txi = tile - tyi * f.tiles_x;
     const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
-    const uint32_t beg = tile_off[tile], end = tile_off[tile + 1];
+    const bool binned = counters[VF_CNT_PAIRS] != 0u;      // no pairs: k_binsort left tile_off untouched
+    const uint32_t beg = binned ? tile_off[tile] : 0u, end = binned ? tile_off[tile + 1] : 0u;
     const bool depth = f.depth != 0;
     const unsigned long long empty = depth ? ~0ull : 0ull;
     const int lx = (int)(tid & 15u), ly = (int)(tid >> 4);

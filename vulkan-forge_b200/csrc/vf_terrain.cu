@@ -400,7 +400,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaLaunchCooperativeKernel((const void*)k_binsort, dim3(binsort_ctas), dim3(256), args, 0, s->stream));
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
-    k_raster<<<s->n_tiles, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
+    k_raster<<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
                                                 s->d_sorted, s->d_counters, clear, frame, d_vis);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());

@@ -510,8 +510,8 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     __shared__ unsigned long long s_key[VF_TILE * VF_TILE];
     __shared__ float s_thr[256];
     const uint32_t tid = threadIdx.x;
-    const uint32_t tile = blockIdx.x;
-    const uint32_t tyi = tile / f.tiles_x, txi = tile - tyi * f.tiles_x;
+    const uint32_t tyi = blockIdx.y, txi = blockIdx.x;      // grid = tiles_x x tiles_y
+    const uint32_t tile = tyi * f.tiles_x + txi;
     const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
     const bool binned = counters[VF_CNT_PAIRS] != 0u;      // no pairs: k_binsort left tile_off untouched
     const uint32_t beg = binned ? tile_off[tile] : 0u, end = binned ? tile_off[tile + 1] : 0u;

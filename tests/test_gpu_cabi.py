@@ -87,3 +87,55 @@ def test_cabi_height_image_and_png(lib, tmp_path):
     assert lib.vf_png_write(p, _p(img, C.c_uint8), 50, 40) == 0
     from PIL import Image
     assert np.array_equal(np.asarray(Image.open(p.decode())), img)
+
+
+def _scene_frame(lib, W, H, G, dem, u, mode, depth, lo, hi):
+    scene = C.c_void_p()
+    assert lib.vf_scene_create(W, H, G, 0, 0, C.byref(scene)) == 0, lib.vf_last_error()
+    assert lib.vf_scene_set_height_f32(scene, _p(dem, C.c_float), dem.shape[1], dem.shape[0]) == 0
+    assert lib.vf_scene_set_uniforms(scene, _p(u, C.c_float)) == 0
+    assert lib.vf_scene_set_mode(scene, mode, depth, C.c_float(lo), C.c_float(hi)) == 0
+    out = np.zeros((H, W, 4), np.uint8)
+    assert lib.vf_scene_render_rgba(scene, _p(out, C.c_uint8)) == 0, lib.vf_last_error()
+    lib.vf_scene_destroy(scene)
+    return out
+
+
+@pytest.mark.parametrize("kind", ["sheared", "ortho"])
+def test_cabi_custom_matrices(lib, oracle, luts, synthetic_dem, kind):
+    """Uniform blocks a foreign host may hand over that the camera API never produces: a sheared
+    projection (general matrices: tiled k_geom) and a symmetric orthographic one (w == 1: the
+    sparse form of k_geom_march).  Both bit-identical to the oracle in NORTHSTAR mode."""
+    W, H, G = 200, 150, 128
+    dem = synthetic_dem(5, G)
+    u = oracle.look_at_uniforms(W, H, (2.5, 2.0, 2.0)).copy()
+    if kind == "sheared":
+        u[16 + 4] = np.float32(0.15)          # P[4]: x += 0.15 * y_view
+        u[16 + 1] = np.float32(-0.05)         # P[1]
+    else:
+        P = np.zeros(16, np.float32)          # column-major symmetric orthographic, depth 0..1
+        P[0], P[5], P[10], P[14], P[15] = 0.45, 0.6, -1.0 / 20.0, 0.0, 1.0
+        u[16:32] = P
+    for depth in (0, 1):
+        got = _scene_frame(lib, W, H, G, dem, u, 1, depth, -0.3, 0.4)
+        ref = oracle.render_terrain(W, H, G, dem, u, luts["viridis"], mode=oracle.MODE_NORTHSTAR, depth=bool(depth),
+                                    h_min=-0.3, h_max=0.4)
+        assert (ref[..., :3] != ref[0, 0, :3]).any(), "test camera sees nothing"
+        assert np.array_equal(got, ref), f"{kind} depth={depth}: {(got != ref).any(-1).sum()} pixels differ"
+
+
+def test_cabi_march_equals_tiled_geometry(lib, synthetic_dem, monkeypatch):
+    """k_geom_march (persistent warp workers) and the tiled k_geom (VF_GEOM_TILED=1) write the same
+    visibility: frames are byte-identical, fine grid and coarse grid, with and without depth."""
+    for (W, H, G, seed) in [(320, 200, 512, 3), (160, 120, 9, 4), (257, 131, 100, 6)]:
+        dem = synthetic_dem(seed, G)
+        import vf_oracle as o
+        u = o.look_at_uniforms(W, H, (3.0, 1.2, -2.0))
+        for mode in (0, 1):
+            for depth in (0, 1):
+                monkeypatch.delenv("VF_GEOM_TILED", raising=False)
+                a = _scene_frame(lib, W, H, G, dem, u, mode, depth, -0.3, 0.4)
+                monkeypatch.setenv("VF_GEOM_TILED", "1")
+                b = _scene_frame(lib, W, H, G, dem, u, mode, depth, -0.3, 0.4)
+                monkeypatch.delenv("VF_GEOM_TILED", raising=False)
+                assert np.array_equal(a, b), (W, H, G, mode, depth)

@@ -9,7 +9,7 @@
 #include <vector>
 
 #include "vf_internal.h"
-#include "vf_geom_march.cuh"
+#include "vf_geom_split.cuh"
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
 typedef CUresult (*vf_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -48,7 +48,10 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
+    uint32_t* d_cellq = nullptr; uint32_t cell_capacity = 0;      // k_geom_cull -> k_cells (cell ids)
+    uint32_t* d_needleq = nullptr; uint32_t needle_capacity = 0;  // k_cells -> k_needles (prim ids)
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
+    alignas(64) CUtensorMap dem_map_gc;  // same tensor, box 36x17 floats (k_geom_cull)
     alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
     bool use_tma = false;                // grid == DEM with identity texel mapping
     uint32_t* d_flag = nullptr;
@@ -72,6 +75,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
     cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag);
+    cudaFree(s->d_cellq); cudaFree(s->d_needleq);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -89,6 +93,14 @@ static int scene_alloc_pairs(vf_scene* s, uint32_t capacity) {
     VF_CUDA(cudaMalloc(&s->d_pair_prim, (size_t)capacity * 4));
     VF_CUDA(cudaMalloc(&s->d_sorted, (size_t)capacity * 4));
     s->capacity = capacity;
+    return VF_OK;
+}
+
+static int scene_alloc_queue(uint32_t** q, uint32_t* cap, uint32_t capacity) {
+    cudaFree(*q);
+    *q = nullptr;
+    VF_CUDA(cudaMalloc(q, (size_t)capacity * 4));
+    *cap = capacity;
     return VF_OK;
 }
 
@@ -150,6 +162,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     s->use_tma = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
     memset(&s->dem_map_gm, 0, sizeof s->dem_map_gm);
+    memset(&s->dem_map_gc, 0, sizeof s->dem_map_gc);
     if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
         if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
         const uint32_t one = 1u;
@@ -170,7 +183,11 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
             const CUresult cr2 = tmap_encoder()(&s->dem_map_gm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box_gm, estr,
                                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            s->use_tma = cr == CUDA_SUCCESS && cr2 == CUDA_SUCCESS;
+            const cuuint32_t box_gc[2] = {VF_GM_BOX_X, VF_GC_VROWS};
+            const CUresult cr3 = tmap_encoder()(&s->dem_map_gc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box_gc, estr,
+                                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            s->use_tma = cr == CUDA_SUCCESS && cr2 == CUDA_SUCCESS && cr3 == CUDA_SUCCESS;
         }
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
@@ -210,7 +227,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     SC(cudaMalloc(&s->d_frame, (size_t)s->n_slots * w * h * 4));
     SC(cudaMalloc(&s->d_tile_count, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4));
     s->d_counters = s->d_tile_count + s->n_tiles;
-    SC(cudaMalloc(&s->d_tile_off, ((size_t)s->n_tiles + 3) * 4));
+    SC(cudaMalloc(&s->d_tile_off, ((size_t)s->n_tiles + 5) * 4));   // + 4 high-water marks
     s->d_maxpairs = s->d_tile_off + s->n_tiles + 1;
     SC(cudaMalloc(&s->d_tile_cursor, (size_t)s->n_tiles * 4));
     SC(cudaHostAlloc(&s->h_counters, 64 * VF_CNT_WORDS * 4, cudaHostAllocDefault));
@@ -223,6 +240,11 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>(cap, 1u << 30));
     if (rc) { scene_free(s); return rc; }
     rc = scene_alloc_big(s, 1u << 20);
+    if (rc) { scene_free(s); return rc; }
+    const uint64_t cells = (uint64_t)(grid - 1) * (grid - 1);
+    rc = scene_alloc_queue(&s->d_cellq, &s->cell_capacity, (uint32_t)std::min<uint64_t>(cells + 32, 1u << 22));
+    if (rc) { scene_free(s); return rc; }
+    rc = scene_alloc_queue(&s->d_needleq, &s->needle_capacity, (uint32_t)std::min<uint64_t>(2 * cells + 32, 1u << 21));
     if (rc) { scene_free(s); return rc; }
     if (cudaMalloc(&s->d_visbuf, (size_t)w * h * 8) != cudaSuccess) {
         scene_free(s);
@@ -324,6 +346,50 @@ static uint32_t clear_rgba8() {
     return enc(0.02f) | (enc(0.02f) << 8) | (enc(0.03f) << 16) | 0xff000000u;
 }
 
+// k_geom_cull -> k_cells -> k_needles (vf_geom_split.cuh).  Rows per task shrink on coarse grids so
+// that every warp of the machine gets a few tasks.
+static int launch_geom_split(vf_scene* s, const VfFrame& f) {
+    static int sm_count = 0, cull_per_sm = 3;
+    const size_t smem = VF_GC_WARPS * sizeof(VfGcWarp);
+    if (!sm_count) {
+        int dev = 0;
+        VF_CUDA(cudaGetDevice(&dev));
+        VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cull_per_sm, k_geom_cull<true, false>, VF_GC_WARPS * 32, smem));
+        cull_per_sm = std::max(cull_per_sm, 1);
+    }
+    const uint32_t gm = s->G - 1;
+    const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
+    const uint32_t workers = (uint32_t)sm_count * (uint32_t)cull_per_sm * VF_GC_WARPS;
+    uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
+    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GC_ROWS);
+    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
+    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * (uint32_t)cull_per_sm, (ntasks + VF_GC_WARPS - 1) / VF_GC_WARPS);
+#define VF_GC_LAUNCH(T, S) k_geom_cull<T, S><<<ctas, VF_GC_WARPS * 32, smem, s->stream>>>( \
+        f, s->dem_map_gc, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_counters, rows)
+    const bool shipped = f.mode == VF_MODE_SHIPPED;
+    if (s->use_tma) { if (shipped) VF_GC_LAUNCH(true, true); else VF_GC_LAUNCH(true, false); }
+    else            { if (shipped) VF_GC_LAUNCH(false, true); else VF_GC_LAUNCH(false, false); }
+#undef VF_GC_LAUNCH
+    const uint32_t g2 = (uint32_t)sm_count * 8u;
+    if (f.depth) {
+        k_cells<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_visbuf, s->d_needleq,
+                                                 s->needle_capacity, s->d_big, s->big_capacity, s->d_counters, s->d_maxpairs);
+        k_needles<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_needleq, s->needle_capacity, s->d_visbuf,
+                                                   s->d_counters, s->d_maxpairs);
+    } else {
+        k_cells<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_visbuf, s->d_needleq,
+                                                  s->needle_capacity, s->d_big, s->big_capacity, s->d_counters, s->d_maxpairs);
+        k_needles<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_needleq, s->needle_capacity, s->d_visbuf,
+                                                    s->d_counters, s->d_maxpairs);
+    }
+    return VF_OK;
+}
+
 // k_geom_march: persistent grid of warp workers; rows per task shrink on coarse grids so that every
 // warp of the machine gets a few tasks
 static int launch_geom_march(vf_scene* s, const VfFrame& f) {
@@ -380,7 +446,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
             k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
                 f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     } else {
-        int rc = launch_geom_march(s, f);
+        int rc = getenv("VF_GEOM_FUSED") ? launch_geom_march(s, f) : launch_geom_split(s, f);
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
@@ -410,7 +476,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
 // h_counters layout: [0..VF_CNT_WORDS) last frame's counters, then the high-water marks (pairs, queued prims)
 static int scene_fetch_counters(vf_scene* s) {
     VF_CUDA(cudaMemcpyAsync(s->h_counters, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
-    VF_CUDA(cudaMemcpyAsync(s->h_counters + VF_CNT_WORDS, s->d_maxpairs, 8, cudaMemcpyDeviceToHost, s->stream));
+    VF_CUDA(cudaMemcpyAsync(s->h_counters + VF_CNT_WORDS, s->d_maxpairs, 16, cudaMemcpyDeviceToHost, s->stream));
     return VF_OK;
 }
 
@@ -439,7 +505,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
     if (rc) return rc;
     const size_t fbytes = (size_t)s->W * s->H * 4;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 8, s->stream));
+        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
         for (int k = 0; k < n; ++k) {
             const int slot = k % VF_MAX_SLOTS;
             if (out_host && k >= VF_MAX_SLOTS) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
@@ -458,7 +524,17 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
         const uint32_t need = s->h_counters[VF_CNT_WORDS], need_big = s->h_counters[VF_CNT_WORDS + 1];
-        if (need <= s->capacity && need_big <= s->big_capacity) return scene_finish_stats(s);
+        const uint32_t need_cells = s->h_counters[VF_CNT_WORDS + 2], need_needles = s->h_counters[VF_CNT_WORDS + 3];
+        if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cell_capacity &&
+            need_needles <= s->needle_capacity) return scene_finish_stats(s);
+        if (need_cells > s->cell_capacity) {
+            rc = scene_alloc_queue(&s->d_cellq, &s->cell_capacity, need_cells + need_cells / 4 + 1024);
+            if (rc) return rc;
+        }
+        if (need_needles > s->needle_capacity) {
+            rc = scene_alloc_queue(&s->d_needleq, &s->needle_capacity, need_needles + need_needles / 4 + 1024);
+            if (rc) return rc;
+        }
         // an overflowed frame left stale keys in the visibility buffer only if k_raster did not run
         // to completion; it always does, so the buffer is clean and the call can simply be repeated
         if (need > (1u << 30)) return vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);

@@ -48,8 +48,8 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
-    uint32_t* d_cellq = nullptr; uint32_t cell_capacity = 0;      // k_geom_cull -> k_cells (cell ids)
-    uint32_t* d_needleq = nullptr; uint32_t needle_capacity = 0;  // k_cells -> k_needles (prim ids)
+    VfCellQ cellq = {nullptr, nullptr, nullptr, 0};       // k_geom_cull -> k_cells
+    VfNeedleQ needleq = {nullptr, nullptr, nullptr, 0};   // k_cells -> k_needles
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
     alignas(64) CUtensorMap dem_map_gc;  // same tensor, box 36x17 floats (k_geom_cull)
     alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
@@ -75,7 +75,8 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
     cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag);
-    cudaFree(s->d_cellq); cudaFree(s->d_needleq);
+    cudaFree(s->cellq.id); cudaFree(s->cellq.xy); cudaFree(s->cellq.z);
+    cudaFree(s->needleq.prim); cudaFree(s->needleq.xy); cudaFree(s->needleq.z);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -96,11 +97,15 @@ static int scene_alloc_pairs(vf_scene* s, uint32_t capacity) {
     return VF_OK;
 }
 
-static int scene_alloc_queue(uint32_t** q, uint32_t* cap, uint32_t capacity) {
-    cudaFree(*q);
-    *q = nullptr;
-    VF_CUDA(cudaMalloc(q, (size_t)capacity * 4));
-    *cap = capacity;
+// structure-of-arrays queue: ids, `planes` int32 planes of coordinates, planes / 2 float planes of z
+template <typename Q>
+static int scene_alloc_queue(Q* q, uint32_t** ids, int planes, uint32_t capacity) {
+    cudaFree(*ids); cudaFree(q->xy); cudaFree(q->z);
+    *ids = nullptr; q->xy = nullptr; q->z = nullptr; q->cap = 0;
+    VF_CUDA(cudaMalloc(ids, (size_t)capacity * 4));
+    VF_CUDA(cudaMalloc(&q->xy, (size_t)capacity * 4 * planes));
+    VF_CUDA(cudaMalloc(&q->z, (size_t)capacity * 4 * (planes / 2)));
+    q->cap = capacity;
     return VF_OK;
 }
 
@@ -242,9 +247,9 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     rc = scene_alloc_big(s, 1u << 20);
     if (rc) { scene_free(s); return rc; }
     const uint64_t cells = (uint64_t)(grid - 1) * (grid - 1);
-    rc = scene_alloc_queue(&s->d_cellq, &s->cell_capacity, (uint32_t)std::min<uint64_t>(cells + 32, 1u << 22));
+    rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, (uint32_t)std::min<uint64_t>(cells + 32, 1u << 21));
     if (rc) { scene_free(s); return rc; }
-    rc = scene_alloc_queue(&s->d_needleq, &s->needle_capacity, (uint32_t)std::min<uint64_t>(2 * cells + 32, 1u << 21));
+    rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, (uint32_t)std::min<uint64_t>(2 * cells + 32, 1u << 20));
     if (rc) { scene_free(s); return rc; }
     if (cudaMalloc(&s->d_visbuf, (size_t)w * h * 8) != cudaSuccess) {
         scene_free(s);
@@ -348,44 +353,49 @@ static uint32_t clear_rgba8() {
 
 // k_geom_cull -> k_cells -> k_needles (vf_geom_split.cuh).  Rows per task shrink on coarse grids so
 // that every warp of the machine gets a few tasks.
+template <bool T, bool D, bool S>
+static int launch_cull(vf_scene* s, const VfFrame& f, int sm_count) {
+    static int per_sm = 0;
+    const size_t smem = VF_GC_WARPS * sizeof(VfGcWarpT<D>);
+    if (!per_sm) {
+        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_geom_cull<T, D, S>, VF_GC_WARPS * 32, smem));
+        per_sm = std::max(per_sm, 1);
+    }
+    const uint32_t gm = s->G - 1;
+    const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
+    const uint32_t workers = (uint32_t)sm_count * (uint32_t)per_sm * VF_GC_WARPS;
+    uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
+    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GC_ROWS);
+    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
+    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * (uint32_t)per_sm, (ntasks + VF_GC_WARPS - 1) / VF_GC_WARPS);
+    k_geom_cull<T, D, S><<<ctas, VF_GC_WARPS * 32, smem, s->stream>>>(f, s->dem_map_gc, s->d_axis, s->d_dem, s->cellq, s->d_counters, rows);
+    return VF_OK;
+}
+
 static int launch_geom_split(vf_scene* s, const VfFrame& f) {
-    static int sm_count = 0, cull_per_sm = 3;
-    const size_t smem = VF_GC_WARPS * sizeof(VfGcWarp);
+    static int sm_count = 0;
     if (!sm_count) {
         int dev = 0;
         VF_CUDA(cudaGetDevice(&dev));
         VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cull_per_sm, k_geom_cull<true, false>, VF_GC_WARPS * 32, smem));
-        cull_per_sm = std::max(cull_per_sm, 1);
     }
-    const uint32_t gm = s->G - 1;
-    const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
-    const uint32_t workers = (uint32_t)sm_count * (uint32_t)cull_per_sm * VF_GC_WARPS;
-    uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
-    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GC_ROWS);
-    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
-    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * (uint32_t)cull_per_sm, (ntasks + VF_GC_WARPS - 1) / VF_GC_WARPS);
-#define VF_GC_LAUNCH(T, S) k_geom_cull<T, S><<<ctas, VF_GC_WARPS * 32, smem, s->stream>>>( \
-        f, s->dem_map_gc, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_counters, rows)
     const bool shipped = f.mode == VF_MODE_SHIPPED;
-    if (s->use_tma) { if (shipped) VF_GC_LAUNCH(true, true); else VF_GC_LAUNCH(true, false); }
-    else            { if (shipped) VF_GC_LAUNCH(false, true); else VF_GC_LAUNCH(false, false); }
-#undef VF_GC_LAUNCH
+    int rc;
+#define VF_GC_PICK(T, D) (shipped ? launch_cull<T, D, true>(s, f, sm_count) : launch_cull<T, D, false>(s, f, sm_count))
+    if (s->use_tma) rc = f.depth ? VF_GC_PICK(true, true) : VF_GC_PICK(true, false);
+    else            rc = f.depth ? VF_GC_PICK(false, true) : VF_GC_PICK(false, false);
+#undef VF_GC_PICK
+    if (rc) return rc;
     const uint32_t g2 = (uint32_t)sm_count * 8u;
     if (f.depth) {
-        k_cells<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_visbuf, s->d_needleq,
-                                                 s->needle_capacity, s->d_big, s->big_capacity, s->d_counters, s->d_maxpairs);
-        k_needles<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_needleq, s->needle_capacity, s->d_visbuf,
-                                                   s->d_counters, s->d_maxpairs);
+        k_cells<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->cellq, s->d_visbuf, s->needleq, s->d_big,
+                                                 s->big_capacity, s->d_counters, s->d_maxpairs);
+        k_needles<true><<<g2, 256, 0, s->stream>>>(f, s->needleq, s->d_visbuf, s->d_counters, s->d_maxpairs);
     } else {
-        k_cells<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_cellq, s->cell_capacity, s->d_visbuf, s->d_needleq,
-                                                  s->needle_capacity, s->d_big, s->big_capacity, s->d_counters, s->d_maxpairs);
-        k_needles<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_needleq, s->needle_capacity, s->d_visbuf,
-                                                    s->d_counters, s->d_maxpairs);
+        k_cells<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->cellq, s->d_visbuf, s->needleq, s->d_big,
+                                                  s->big_capacity, s->d_counters, s->d_maxpairs);
+        k_needles<false><<<g2, 256, 0, s->stream>>>(f, s->needleq, s->d_visbuf, s->d_counters, s->d_maxpairs);
     }
     return VF_OK;
 }
@@ -446,7 +456,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
             k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
                 f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     } else {
-        int rc = getenv("VF_GEOM_FUSED") ? launch_geom_march(s, f) : launch_geom_split(s, f);
+        int rc = getenv("VF_GEOM_SPLIT") ? launch_geom_split(s, f) : launch_geom_march(s, f);   // A/B switch
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
@@ -525,14 +535,14 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
         const uint32_t need = s->h_counters[VF_CNT_WORDS], need_big = s->h_counters[VF_CNT_WORDS + 1];
         const uint32_t need_cells = s->h_counters[VF_CNT_WORDS + 2], need_needles = s->h_counters[VF_CNT_WORDS + 3];
-        if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cell_capacity &&
-            need_needles <= s->needle_capacity) return scene_finish_stats(s);
-        if (need_cells > s->cell_capacity) {
-            rc = scene_alloc_queue(&s->d_cellq, &s->cell_capacity, need_cells + need_cells / 4 + 1024);
+        if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cellq.cap &&
+            need_needles <= s->needleq.cap) return scene_finish_stats(s);
+        if (need_cells > s->cellq.cap) {
+            rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, need_cells + need_cells / 4 + 1024);
             if (rc) return rc;
         }
-        if (need_needles > s->needle_capacity) {
-            rc = scene_alloc_queue(&s->d_needleq, &s->needle_capacity, need_needles + need_needles / 4 + 1024);
+        if (need_needles > s->needleq.cap) {
+            rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, need_needles + need_needles / 4 + 1024);
             if (rc) return rc;
         }
         // an overflowed frame left stale keys in the visibility buffer only if k_raster did not run

@@ -156,7 +156,7 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                                 int64_t ed[3];
                                 if (vf_edges_at(es, dx, dy, ed)) vf_gm_emit<DEPTH>(f, vis, t, es, prim, x0 + dx, y0 + dy, ed);
                             }
-                    } else if (npx <= VF_MEDIUM_MAX) {
+                    } else if (vf_serial_ok(t, bw, bh)) {
                         to_long = true;
                     } else {
                         to_big = true;

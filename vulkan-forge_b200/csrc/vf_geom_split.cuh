@@ -346,7 +346,7 @@ k_cells(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, cons
                             int64_t ed[3];
                             if (vf_edges_at(es, dx, dy, ed)) vf_gm_emit<DEPTH>(f, vis, t, es, 2u * cell + k, x0 + dx, y0 + dy, ed);
                         }
-                } else if (npx <= VF_MEDIUM_MAX) {
+                } else if (vf_serial_ok(t, bw, bh)) {
                     to_long[k] = true;
                 } else {
                     to_big[k] = true;

@@ -50,7 +50,8 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_GEOM_VX (VF_GEOM_TX + 1)
 #define VF_GEOM_VY (VF_GEOM_TY + 1)
 #define VF_MICRO_MAX 4         // pixel-centre count up to which one thread rasterises a triangle
-#define VF_MEDIUM_MAX 4096     // bbox pixels up to which one thread walks the runs (queued, packed); larger -> binned
+#define VF_SERIAL_LINES 256    // one thread walks the runs of a triangle with at most this many lines of its
+#define VF_SERIAL_AREA 4096    // shorter bbox axis and at most this many pixels of area; larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
 enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_CELLS = 6, VF_CNT_NEEDLES = 7, VF_CNT_WORDS = 8 };
@@ -95,6 +96,12 @@ __device__ __forceinline__ void vf_prim_vertices(const VfFrame& f, const VfAxis*
 __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool depth, uint32_t prim, float zf) {
     if (depth) atomicMin(key64, ((unsigned long long)__float_as_uint(zf) << 32) | prim);
     else atomicMax(reinterpret_cast<uint32_t*>(key64), prim + 1u);   // low word (little endian)
+}
+
+// Work of the run rasteriser follows lines + covered samples, not the bbox: a needle 40 pixels across
+// and 400 long with 20 pixels of area is cheap, a fat triangle of the same bbox is not.
+__device__ __forceinline__ bool vf_serial_ok(const VfSubTri& t, int bw, int bh) {
+    return min(bw, bh) <= VF_SERIAL_LINES && (-vf_area2(t) >> 17) <= (int64_t)VF_SERIAL_AREA;   // area2 is in (1/256 px)^2 * 2
 }
 
 // ---------------------------------------------------------------------------------------
@@ -288,7 +295,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
                                     int64_t ed[3];
                                     if (vf_edges_at(es, dx, dy, ed)) emit_sample(t, es, prim, x0 + dx, y0 + dy, ed);
                                 }
-                        } else if (npx <= VF_MEDIUM_MAX) {
+                        } else if (vf_serial_ok(t, bw, bh)) {
                             to_thin = true;
                         } else {
                             to_big = true;

@@ -125,6 +125,13 @@ int vf_scene_auto_height_range(vf_scene *s, float *h_min, float *h_max);
 int vf_scene_render_rgba(vf_scene *s, uint8_t *out_rgba_host);
 /* n frames, one uniform block each, frames gathered to host (pinned memory recommended) */
 int vf_scene_render_batch(vf_scene *s, const float *u44xn, int n, uint8_t *out_rgba_host);
+/* Pipelined variants (batches of independent frames): the upload goes to a second
+ * device image on its own stream while frames of the current image render; the batch call returns
+ * once everything is enqueued.  Host buffers must be pinned and stay untouched until vf_scene_wait
+ * (output) / the next vf_scene_wait after the batch that uses them (height).  At most 4 batches in flight. */
+int vf_scene_set_height_f32_async(vf_scene *s, const float *host_pinned, uint32_t w, uint32_t h);
+int vf_scene_render_batch_async(vf_scene *s, const float *u44xn, int n, uint8_t *out_rgba_host_pinned, int *ticket);
+int vf_scene_wait(vf_scene *s, int ticket);
 /* n frames left in device memory (no D2H); for kernel-only timing */
 int vf_scene_render_device(vf_scene *s, const float *u44xn, int n);
 /* visibility of the last frame: per pixel 0 = clear colour, else primitive id + 1 */

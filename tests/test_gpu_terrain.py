@@ -274,3 +274,33 @@ def test_tma_staging_matches_gather_path(ext, synthetic_dem, monkeypatch):
     sc.set_height_from_r32f(dem)
     sc.render_rgba()
     assert sc.render_metrics()["tma"] == 0
+
+
+def test_pipelined_batches_equal_synchronous(ext, vf, synthetic_dem):
+    """set_height_from_r32f_async / render_batch_rgba_async / collect: uploads alternate between two
+    DEMs while earlier batches are still in flight; every batch must equal the synchronous result
+    for the DEM that was current when it was submitted."""
+    W, H, G = 320, 200, 256
+    dems = [synthetic_dem(21, G), synthetic_dem(22, G)]
+    cams = vf.orbit_cameras(12)[:5]
+    sc = ext.Scene(W, H, grid=G, colormap="terrain")
+    sc.set_shading("northstar", depth=True)
+    sc.set_height_range(-0.3, 0.4)
+    want = []
+    for d in dems:
+        sc.set_height_from_r32f(d)
+        want.append(sc.render_batch_rgba(cams).copy())
+    assert not np.array_equal(want[0], want[1])
+    tickets = []
+    for k in range(6):
+        sc.set_height_from_r32f_async(dems[k & 1])
+        tickets.append((k & 1, sc.render_batch_rgba_async(cams)))
+        if len(tickets) == 3:                                   # three batches in flight at most here
+            which, tk = tickets.pop(0)
+            assert np.array_equal(sc.collect(tk), want[which]), k
+    for which, tk in tickets:
+        assert np.array_equal(sc.collect(tk), want[which])
+    with pytest.raises(ValueError):
+        sc.collect(0)
+    # the synchronous path still works afterwards and sees the last uploaded image
+    assert np.array_equal(sc.render_batch_rgba(cams), want[1])

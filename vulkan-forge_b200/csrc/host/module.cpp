@@ -284,6 +284,37 @@ public:
         }
         return out;
     }
+    // ---- pipelined batches: upload k+1 and batch k overlap; see include/vf_cuda.h ----
+    void set_height_from_r32f_async(py::object height_r32f) {
+        if (!py::isinstance<py::array>(height_r32f)) throw py::type_error("argument 'height_r32f': expected a numpy float32 array");
+        py::array arr = py::reinterpret_borrow<py::array>(height_r32f);
+        if (arr.ndim() != 2 || !arr.dtype().is(py::dtype::of<float>()))
+            throw py::type_error("argument 'height_r32f': expected a 2-D numpy array of dtype float32");
+        if (!(arr.flags() & py::array::c_style)) throw std::runtime_error("height must be C-contiguous float32[H,W]");
+        held_height_ = arr;                                   // the copy is in flight after this call returns
+        check(vf_scene_set_height_f32_async(scene_, static_cast<const float*>(arr.data()), (uint32_t)arr.shape(1), (uint32_t)arr.shape(0)));
+    }
+    int render_batch_rgba_async(py::object cameras) {
+        const std::vector<float> blocks = camera_blocks(cameras);
+        const int n = (int)(blocks.size() / 44);
+        if (n == 0) throw py::value_error("no cameras given");
+        auto out = pinned_array<uint8_t>({(py::ssize_t)n, (py::ssize_t)height_, (py::ssize_t)width_, 4});
+        int ticket = -1;
+        check(vf_scene_render_batch_async(scene_, blocks.data(), n, out.mutable_data(), &ticket));
+        in_flight_[ticket] = out;
+        return ticket;
+    }
+    py::array_t<uint8_t> collect(int ticket) {
+        auto it = in_flight_.find(ticket);
+        if (it == in_flight_.end()) throw py::value_error("unknown ticket");
+        {
+            py::gil_scoped_release nogil;
+            check(vf_scene_wait(scene_, ticket));
+        }
+        py::array_t<uint8_t> out = it->second;
+        in_flight_.erase(it);
+        return out;
+    }
     // frames stay on the device; returns elapsed milliseconds (host clock around a synchronous call)
     double render_batch_device(py::object cameras) {
         const std::vector<float> blocks = camera_blocks(cameras);
@@ -324,6 +355,8 @@ private:
     uint32_t width_, height_, grid_ = 128;
     bool spike_, lut_unorm_ = false;
     vf_scene* scene_ = nullptr;
+    py::object held_height_;
+    std::map<int, py::array_t<uint8_t>> in_flight_;
     Globals globals_;
     M4 view_, proj_;
     int mode_ = VF_MODE_SHIPPED;

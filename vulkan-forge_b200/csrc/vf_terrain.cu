@@ -54,11 +54,24 @@ struct vf_scene {
     alignas(64) CUtensorMap dem_map_gc;  // same tensor, box 36x17 floats (k_geom_cull)
     alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
     bool use_tma = false;                // grid == DEM with identity texel mapping
+    // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
+    // front image render; swapped in by the next submit
+    float* d_dem_back = nullptr;
+    alignas(64) CUtensorMap dem_map_b, dem_map_gm_b, dem_map_gc_b;
+    bool back_valid = false, back_pending = false, front_released_once = false;
+    cudaStream_t upload_stream = nullptr;
+    cudaEvent_t ev_uploaded = nullptr, ev_front_released = nullptr;
+    // batches in flight (vf_scene_render_batch_async): completion event on the copy stream, the
+    // high-water marks of the batch in a pinned slot, and what is needed to redo it after growing a buffer
+    struct Ticket { cudaEvent_t done = nullptr; bool busy = false; std::vector<float> u; int n = 0; uint8_t* out = nullptr; };
+    Ticket tickets[4];
+    bool slot_used[2] = {false, false};
     uint32_t* d_flag = nullptr;
     uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
     uint32_t* d_pair_tile = nullptr; uint32_t* d_pair_prim = nullptr; uint32_t* d_sorted = nullptr;
     uint32_t capacity = 0;
-    uint32_t* h_counters = nullptr;      // pinned, VF_CNT_WORDS per slot (max 64 slots)
+    uint32_t* h_counters = nullptr;      // pinned: 2*VF_CNT_WORDS words per batch slot (counters, high-water marks)
+    uint32_t h_counters_last[VF_CNT_WORDS] = {0};
     cudaStream_t stream = nullptr; bool own_stream = false;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -75,6 +88,11 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
     cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag);
+    cudaFree(s->d_dem_back);
+    if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
+    if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
+    if (s->ev_front_released) cudaEventDestroy(s->ev_front_released);
+    for (auto& t : s->tickets) if (t.done) cudaEventDestroy(t.done);
     cudaFree(s->cellq.id); cudaFree(s->cellq.xy); cudaFree(s->cellq.z);
     cudaFree(s->needleq.prim); cudaFree(s->needleq.xy); cudaFree(s->needleq.z);
     if (s->h_counters) cudaFreeHost(s->h_counters);
@@ -148,13 +166,32 @@ static int scene_rebuild_axis(vf_scene* s) {
     return VF_OK;
 }
 
+// the three 2-D tiled maps over a DEM image: boxes of k_geom (36x33), k_geom_march (36x25), k_geom_cull (36x17)
+static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pitch, CUtensorMap* m_tiled, CUtensorMap* m_march,
+                              CUtensorMap* m_cull) {
+    if (!tmap_encoder()) return false;
+    const cuuint64_t gdim[2] = {w, h};
+    const cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4};
+    const cuuint32_t estr[2] = {1, 1};
+    const cuuint32_t boxes[3][2] = {{VF_TMA_BOX_X, VF_TMA_BOX_Y}, {VF_GM_BOX_X, VF_GM_VROWS}, {VF_GM_BOX_X, VF_GC_VROWS}};
+    CUtensorMap* maps[3] = {m_tiled, m_march, m_cull};
+    bool ok = true;
+    for (int k = 0; k < 3; ++k)
+        ok = ok && tmap_encoder()(maps[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, d_dem, gdim, gstride, boxes[k], estr,
+                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+    return ok;
+}
+
 static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "height image cannot be empty");
     const uint32_t pitch = (w + 3u) & ~3u;            // rows start 16-byte aligned (TMA-ready)
+    if (s->upload_stream) VF_CUDA(cudaStreamSynchronize(s->upload_stream));
+    s->back_pending = false;
     if (pitch != s->pitch || h != s->Hd || !s->d_dem) {
         VF_CUDA(cudaStreamSynchronize(s->stream));
-        cudaFree(s->d_dem);
-        s->d_dem = nullptr;
+        cudaFree(s->d_dem); cudaFree(s->d_dem_back);
+        s->d_dem = nullptr; s->d_dem_back = nullptr; s->back_valid = false;
         VF_CUDA(cudaMalloc(&s->d_dem, (size_t)pitch * h * 4));
     }
     s->Wd = w; s->Hd = h; s->pitch = pitch;
@@ -177,22 +214,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
         VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (flag == 1u) {
-            const cuuint64_t gdim[2] = {w, h};
-            const cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4};
-            const cuuint32_t box[2] = {VF_TMA_BOX_X, VF_TMA_BOX_Y};
-            const cuuint32_t estr[2] = {1, 1};
-            const CUresult cr = tmap_encoder()(&s->dem_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box, estr,
-                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            const cuuint32_t box_gm[2] = {VF_GM_BOX_X, VF_GM_VROWS};
-            const CUresult cr2 = tmap_encoder()(&s->dem_map_gm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box_gm, estr,
-                                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            const cuuint32_t box_gc[2] = {VF_GM_BOX_X, VF_GC_VROWS};
-            const CUresult cr3 = tmap_encoder()(&s->dem_map_gc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s->d_dem, gdim, gstride, box_gc, estr,
-                                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-            s->use_tma = cr == CUDA_SUCCESS && cr2 == CUDA_SUCCESS && cr3 == CUDA_SUCCESS;
+            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, &s->dem_map_gm, &s->dem_map_gc);
         }
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
@@ -266,6 +288,8 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
 extern "C" void vf_scene_destroy(vf_scene* s) {
     if (!s) return;
     cudaStreamSynchronize(s->stream);
+    if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);       // batches / uploads still in flight
+    if (s->upload_stream) cudaStreamSynchronize(s->upload_stream);
     scene_free(s);
 }
 
@@ -483,19 +507,12 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     return VF_OK;
 }
 
-// h_counters layout: [0..VF_CNT_WORDS) last frame's counters, then the high-water marks (pairs, queued prims)
-static int scene_fetch_counters(vf_scene* s) {
-    VF_CUDA(cudaMemcpyAsync(s->h_counters, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
-    VF_CUDA(cudaMemcpyAsync(s->h_counters + VF_CNT_WORDS, s->d_maxpairs, 16, cudaMemcpyDeviceToHost, s->stream));
-    return VF_OK;
-}
-
 static int scene_finish_stats(vf_scene* s) {
-    s->stats.bin_pairs = s->h_counters[VF_CNT_PAIRS];
-    s->stats.clipped_prims = s->h_counters[VF_CNT_CLIPPED];
+    s->stats.bin_pairs = s->h_counters_last[VF_CNT_PAIRS];
+    s->stats.clipped_prims = s->h_counters_last[VF_CNT_CLIPPED];
     s->stats.bin_capacity = s->capacity;
     s->stats.tma = s->use_tma ? 1u : 0u;
-    s->stats.big_prims = s->h_counters[VF_CNT_BIG];
+    s->stats.big_prims = s->h_counters_last[VF_CNT_BIG];
     s->stats.tiles = s->n_tiles;
     if (s->timing) {
         VF_CUDA(cudaEventElapsedTime(&s->stats.ms_geom, s->ev[0], s->ev[1]));
@@ -506,58 +523,152 @@ static int scene_finish_stats(vf_scene* s) {
     return VF_OK;
 }
 
-// Renders n frames; out_host may be null (frames stay on the device).  Frame k is rendered into
-// slot k%2 while the copy stream drains slot (k-1)%2 to the host.  If the binning kernel asked
-// for more pairs than the buffer holds, the buffer is grown and the whole call is repeated.
+// frames enqueued from here on read the image uploaded by vf_scene_set_height_f32_async
+static int scene_apply_pending_dem(vf_scene* s) {
+    if (!s->back_pending) return VF_OK;
+    VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_uploaded, 0));
+    VF_CUDA(cudaEventRecord(s->ev_front_released, s->stream));   // every frame of the old image precedes this
+    s->front_released_once = true;
+    std::swap(s->d_dem, s->d_dem_back);
+    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b); std::swap(s->dem_map_gc, s->dem_map_gc_b);
+    s->back_pending = false;
+    return VF_OK;
+}
+
+// Enqueues n frames (+ their D2H copies when out_host is given) and the read-back of the batch's
+// counters into pinned slot `hslot`.  Frame k is rendered into slot k%2 while the copy stream
+// drains the other slot to the host.  Does not wait.
+static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, int hslot) {
+    int rc = scene_apply_pending_dem(s);
+    if (rc) return rc;
+    const size_t fbytes = (size_t)s->W * s->H * 4;
+    VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
+    for (int k = 0; k < n; ++k) {
+        const int slot = k % VF_MAX_SLOTS;
+        if (out_host && s->slot_used[slot]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
+        rc = scene_enqueue(s, u44xn + (size_t)k * 44, slot, d_vis);
+        if (rc) return rc;
+        if (out_host) {
+            VF_CUDA(cudaEventRecord(s->ev_done[slot], s->stream));
+            VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[slot], 0));
+            VF_CUDA(cudaMemcpyAsync(out_host + (size_t)k * fbytes, s->d_frame + (size_t)slot * fbytes,
+                                    fbytes, cudaMemcpyDeviceToHost, s->copy_stream));
+            VF_CUDA(cudaEventRecord(s->ev_copied[slot], s->copy_stream));
+            s->slot_used[slot] = true;
+        }
+    }
+    uint32_t* h = s->h_counters + (size_t)hslot * 2 * VF_CNT_WORDS;
+    VF_CUDA(cudaMemcpyAsync(h, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
+    VF_CUDA(cudaMemcpyAsync(h + VF_CNT_WORDS, s->d_maxpairs, 16, cudaMemcpyDeviceToHost, s->stream));
+    return VF_OK;
+}
+
+// after the batch of pinned slot `hslot` has completed: 0 = fine, 1 = a buffer overflowed and was
+// grown (the batch must be rendered again), < 0 = error code
+static int scene_check_overflow(vf_scene* s, int hslot) {
+    const uint32_t* h = s->h_counters + (size_t)hslot * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
+    const uint32_t need = h[0], need_big = h[1], need_cells = h[2], need_needles = h[3];
+    if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cellq.cap && need_needles <= s->needleq.cap) return 0;
+    VF_CUDA(cudaStreamSynchronize(s->stream));           // nothing in flight may still use the buffers
+    if (need > (1u << 30)) return -vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
+    int rc;
+    if (need > s->capacity) {
+        rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>((uint64_t)need + need / 4 + 1024, 1u << 30));
+        if (rc) return -rc;
+    }
+    if (need_big > s->big_capacity) {
+        rc = scene_alloc_big(s, need_big + need_big / 4 + 1024);
+        if (rc) return -rc;
+    }
+    if (need_cells > s->cellq.cap) {
+        rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, need_cells + need_cells / 4 + 1024);
+        if (rc) return -rc;
+    }
+    if (need_needles > s->needleq.cap) {
+        rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, need_needles + need_needles / 4 + 1024);
+        if (rc) return -rc;
+    }
+    return 1;
+}
+
+// Renders n frames and waits; out_host may be null (frames stay on the device).  If a kernel asked
+// for more queue / pair space than its buffer holds, the buffer is grown and the call is repeated
+// (an overflowed frame leaves a clean visibility buffer: k_raster always runs to completion).
 static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis) {
     if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
     int rc = vf_require_device();
     if (rc) return rc;
-    const size_t fbytes = (size_t)s->W * s->H * 4;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
-        for (int k = 0; k < n; ++k) {
-            const int slot = k % VF_MAX_SLOTS;
-            if (out_host && k >= VF_MAX_SLOTS) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
-            rc = scene_enqueue(s, u44xn + (size_t)k * 44, slot, d_vis);
-            if (rc) return rc;
-            if (out_host) {
-                VF_CUDA(cudaEventRecord(s->ev_done[slot], s->stream));
-                VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[slot], 0));
-                VF_CUDA(cudaMemcpyAsync(out_host + (size_t)k * fbytes, s->d_frame + (size_t)slot * fbytes,
-                                        fbytes, cudaMemcpyDeviceToHost, s->copy_stream));
-                VF_CUDA(cudaEventRecord(s->ev_copied[slot], s->copy_stream));
-            }
-        }
-        rc = scene_fetch_counters(s);
+        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0);
         if (rc) return rc;
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
-        const uint32_t need = s->h_counters[VF_CNT_WORDS], need_big = s->h_counters[VF_CNT_WORDS + 1];
-        const uint32_t need_cells = s->h_counters[VF_CNT_WORDS + 2], need_needles = s->h_counters[VF_CNT_WORDS + 3];
-        if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cellq.cap &&
-            need_needles <= s->needleq.cap) return scene_finish_stats(s);
-        if (need_cells > s->cellq.cap) {
-            rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, need_cells + need_cells / 4 + 1024);
-            if (rc) return rc;
-        }
-        if (need_needles > s->needleq.cap) {
-            rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, need_needles + need_needles / 4 + 1024);
-            if (rc) return rc;
-        }
-        // an overflowed frame left stale keys in the visibility buffer only if k_raster did not run
-        // to completion; it always does, so the buffer is clean and the call can simply be repeated
-        if (need > (1u << 30)) return vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
-        if (need > s->capacity) {
-            rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>((uint64_t)need + need / 4 + 1024, 1u << 30));
-            if (rc) return rc;
-        }
-        if (need_big > s->big_capacity) {
-            rc = scene_alloc_big(s, need_big + need_big / 4 + 1024);
-            if (rc) return rc;
-        }
+        memcpy(s->h_counters_last, s->h_counters, VF_CNT_WORDS * 4);
+        const int ov = scene_check_overflow(s, 0);
+        if (ov < 0) return -ov;
+        if (ov == 0) return scene_finish_stats(s);
     }
     return vf_set_error(VF_E_CUDA, "pair buffer kept overflowing");
+}
+
+// ---- pipelined interface: uploads and batches overlap across calls -------------------------------
+extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
+    if (!s || !host) return vf_set_error(VF_E_INVALID, "null argument");
+    const uint32_t pitch = (w + 3u) & ~3u;
+    if (w != s->Wd || h != s->Hd || pitch != s->pitch || !s->d_dem) return scene_upload_dem(s, host, w, h);   // new size: synchronous path
+    if (!s->upload_stream) {
+        VF_CUDA(cudaStreamCreateWithFlags(&s->upload_stream, cudaStreamNonBlocking));
+        VF_CUDA(cudaEventCreateWithFlags(&s->ev_uploaded, cudaEventDisableTiming));
+        VF_CUDA(cudaEventCreateWithFlags(&s->ev_front_released, cudaEventDisableTiming));
+    }
+    if (!s->d_dem_back) {
+        VF_CUDA(cudaMalloc(&s->d_dem_back, (size_t)pitch * h * 4));
+        s->back_valid = false;
+    }
+    if (!s->back_valid) {
+        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, &s->dem_map_gm_b, &s->dem_map_gc_b))
+            return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
+        s->back_valid = true;
+    }
+    // the back image was the front image of frames submitted before the last swap
+    if (s->front_released_once) VF_CUDA(cudaStreamWaitEvent(s->upload_stream, s->ev_front_released, 0));
+    VF_CUDA(cudaMemcpy2DAsync(s->d_dem_back, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
+                              cudaMemcpyHostToDevice, s->upload_stream));
+    VF_CUDA(cudaEventRecord(s->ev_uploaded, s->upload_stream));
+    s->back_pending = true;
+    return VF_OK;
+}
+
+extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int n, uint8_t* out_rgba_host, int* ticket) {
+    if (!s || !u44xn || n <= 0 || !out_rgba_host || !ticket) return vf_set_error(VF_E_INVALID, "invalid argument");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    int id = -1;
+    for (int k = 0; k < 4; ++k) if (!s->tickets[k].busy) { id = k; break; }
+    if (id < 0) return vf_set_error(VF_E_INVALID, "4 batches already in flight: call vf_scene_wait first");
+    vf_scene::Ticket& t = s->tickets[id];
+    if (!t.done) VF_CUDA(cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming));
+    t.u.assign(u44xn, u44xn + (size_t)n * 44); t.n = n; t.out = out_rgba_host;
+    rc = scene_submit(s, u44xn, n, out_rgba_host, nullptr, 1 + id);
+    if (rc) return rc;
+    // done = counters read back on the render stream and every frame copied on the copy stream
+    VF_CUDA(cudaEventRecord(s->ev_done[0], s->stream));           // reuse as a plain marker: ordered after the read-back
+    VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[0], 0));
+    VF_CUDA(cudaEventRecord(t.done, s->copy_stream));
+    t.busy = true;
+    *ticket = id;
+    return VF_OK;
+}
+
+extern "C" int vf_scene_wait(vf_scene* s, int ticket) {
+    if (!s || ticket < 0 || ticket >= 4 || !s->tickets[ticket].busy) return vf_set_error(VF_E_INVALID, "invalid ticket");
+    vf_scene::Ticket& t = s->tickets[ticket];
+    VF_CUDA(cudaEventSynchronize(t.done));
+    t.busy = false;
+    const int ov = scene_check_overflow(s, 1 + ticket);
+    if (ov < 0) return -ov;
+    if (ov == 1) return scene_render(s, t.u.data(), t.n, t.out, nullptr);   // rare: redo synchronously with the grown buffers
+    return VF_OK;
 }
 
 extern "C" int vf_scene_render_rgba(vf_scene* s, uint8_t* out_rgba_host) {
@@ -591,7 +702,9 @@ int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t p
 extern "C" int vf_scene_auto_height_range(vf_scene* s, float* h_min, float* h_max) {
     if (!s) return vf_set_error(VF_E_INVALID, "null scene");
     float lo, hi;
-    int rc = vf_dem_minmax_device(s->d_dem, s->Wd, s->Hd, s->pitch, 1, &lo, &hi, s->stream);
+    int rc = scene_apply_pending_dem(s);
+    if (rc) return rc;
+    rc = vf_dem_minmax_device(s->d_dem, s->Wd, s->Hd, s->pitch, 1, &lo, &hi, s->stream);
     if (rc) return rc;
     const float guard = lo + 1e-5f;
     hi = hi > guard ? hi : guard;

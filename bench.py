@@ -268,6 +268,12 @@ def main():
         dom_bytes = algo[dom] if algo[dom] else ALGO_BYTES_FRAME
         achieved = dom_bytes / (kmed[dom] * 1e-3) / 1e9
         frame_achieved = ALGO_BYTES_FRAME / (kmed["ms_total"] * 1e-3) / 1e9
+        # Second reading of the same kernel: it is issue-bound, not HBM-bound.  Warp
+        # instructions per launch come from the committed ncu capture, the time is the live one above.
+        issue, winst = None, ncu_traffic({"ms_geom": "k_geom", "ms_raster": "k_raster"}.get(dom, "") + "_warp_inst")
+        if winst and clocks and clocks.get("sm_mhz"):
+            slots = 148 * 4 * clocks["sm_mhz"] * 1e6 * kmed[dom] * 1e-3          # one warp instruction per SM sub-partition per clock
+            issue = {"warp_inst_per_launch": winst, "issue_slots": slots, "frac": winst / slots, "source": "profiles/dram_traffic.json"}
         cpu = None
         if world == 1:                                     # reported at N=1 only
             us = [np.asarray(blocks[i]) for i in range(min(F, 4))]
@@ -289,7 +295,7 @@ def main():
                          "traffic": ncu_traffic({"ms_geom": "k_geom", "ms_bin": "k_bin", "ms_raster": "k_raster"}[dom]),
                          "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kmed[dom],
                          "frame": {"algorithmic_bytes": ALGO_BYTES_FRAME, "ms": kmed["ms_total"], "achieved": frame_achieved, "frac": frame_achieved / peak},
-                         "kernels_ms": kmed},
+                         "kernels_ms": kmed, "issue": issue},
             "cpu_baseline": cpu,
             "clocks": clocks,
         }

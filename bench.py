@@ -45,6 +45,9 @@ class ClockSampler:
 
     def __init__(self, index):
         self.p = None
+        vis = [v.strip() for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
+        if index < len(vis):                               # nvidia-smi counts physical devices (index or UUID both accepted)
+            index = vis[index]
         try:
             self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20"],
                                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)

@@ -3,12 +3,15 @@
 // clip / cull / coverage state of src/terrain/pipeline.rs:107-140 for the implicit grid of
 // src/terrain/mod.rs:553-598).
 //
-//   task     : 32 vertex columns x 25 vertex rows of the grid (31 x 24 cells); tasks are handed
-//              out by one atomic counter, every warp is its own worker
+//   task     : 32 vertex columns x up to 25 vertex rows of the grid (31 x 24 cells); tasks are handed
+//              out in order by one atomic counter, every warp is its own worker.  The row segments
+//              get shorter towards the end of the grid (host-built table), and a worker asks for
+//              its next task only half way through the current one: both keep the finish times of
+//              the 2368 workers close together (measured with VF_GM_DBG + tools/gm_tasks.py)
 //   staging  : the task's 25 x 32 DEM texels are one 2-D TMA box (cp.async.bulk.tensor, 36 texels
 //              wide: a box must start on a 16-byte boundary in global memory, strips start every
-//              31 columns) into the warp's private two-stage ring; the box of task n+1 is in
-//              flight while task n runs
+//              31 columns) into the warp's private two-stage ring; the box of task n+1 is issued
+//              when three quarters of task n are done
 //   march    : lane = vertex column.  The warp walks down the rows; a lane keeps the previous row's
 //              snapped vertex in registers and gets the right-hand neighbour by shuffle, so a cell
 //              costs one vertex stage + two shuffles + one bbox test.  Cells whose bbox holds no
@@ -209,24 +212,37 @@ __global__ void __launch_bounds__(VF_GM_WARPS * 32, 2)
 k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap dem_map,
              const VfAxis* __restrict__ axis, const float* __restrict__ dem,
              unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims, uint32_t big_capacity,
-             uint32_t* __restrict__ counters, uint32_t rows) {
+             uint32_t* __restrict__ counters, const uint2* __restrict__ segtab, uint32_t nsegs,
+             unsigned long long* __restrict__ dbg) {
     extern __shared__ __align__(128) unsigned char vf_gm_smem[];
     const uint32_t lane = threadIdx.x & 31u;
     VfGmWarpT<DEPTH>& w = reinterpret_cast<VfGmWarpT<DEPTH>*>(vf_gm_smem)[threadIdx.x >> 5];
     const uint32_t gm = f.G - 1u;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1u) / VF_GM_QCOLS;
-    const uint32_t nsegs = (gm + rows - 1u) / rows;          // rows (<= VF_GM_ROWS) cell rows per task
+    // A task = one strip of one row segment.  segtab[seg] = (first cell row, cell rows <= VF_GM_ROWS):
+    // the host tapers the segment height towards the end of the grid (vf_terrain.cu), and the
+    // dispenser hands tasks out in order, so the short ones come last and the workers finish together.
     const uint32_t ntasks = nstrips * nsegs;
+    auto decode = [&](uint32_t task, uint32_t& strip, uint32_t& j0, uint32_t& nr) {
+        const uint32_t seg = task / nstrips;
+        strip = task - seg * nstrips;
+        const uint2 e = __ldg(segtab + seg);
+        j0 = e.x; nr = e.y;
+    };
     const uint32_t below = (1u << lane) - 1u;
 
-    // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
+    // The dispenser's answer takes an L2 round trip and the texels of a task another one: the next
+    // task is asked for half way through the current one and its TMA starts at three quarters.
+    // (Asking earlier hides no more latency and leaves every worker with one more task in hand when
+    // the dispenser runs dry, which is what spreads the finish times.)
     auto ask_task = [&]() -> uint32_t { return lane == 0 ? atomicAdd(&counters[VF_CNT_TASK], 1u) : 0u; };
     auto got_task = [&](uint32_t t) -> uint32_t { return __shfl_sync(0xffffffffu, t, 0); };
     auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
         if (TMA && lane == 0 && task < ntasks) {
-            const uint32_t strip = task % nstrips, seg = task / nstrips;
+            uint32_t strip, j0, nr;
+            decode(task, strip, j0, nr);
             vf_mbar_expect_tx(&w.mbar[stage], VF_GM_VROWS * VF_GM_BOX_X * 4u);
-            vf_tma_load_2d(&w.dem[stage][0], &dem_map, (int)((strip * VF_GM_QCOLS) & ~3u), (int)(seg * rows), &w.mbar[stage]);
+            vf_tma_load_2d(&w.dem[stage][0], &dem_map, (int)((strip * VF_GM_QCOLS) & ~3u), (int)j0, &w.mbar[stage]);
         }
     };
     if (TMA) {                                              // thread 0 initialises every warp's pair of barriers
@@ -241,7 +257,6 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
     uint32_t cur = got_task(ask_task());
     issue(cur, 0u);
-    uint32_t nxt = got_task(ask_task());
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
     float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
@@ -252,12 +267,13 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     VF_PIN(exag); VF_PIN(hw); VF_PIN(hh);
 #undef VF_PIN
 
+    unsigned long long t_task = 0ull;
+    if (dbg) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_task)); if (lane == 0) dbg[2u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5))] = t_task; }
     while (cur < ntasks) {
-        issue(nxt, stage ^ 1u);
-        const uint32_t asked = ask_task();                  // becomes `nxt` at the end of this task
-        const uint32_t strip = cur % nstrips, seg = cur / nstrips;
-        const uint32_t i = strip * VF_GM_QCOLS + lane, j0 = seg * rows;
-        const uint32_t nrows = min(rows + 1u, f.G - j0);    // vertex rows of this task
+        uint32_t strip, j0, nr;
+        decode(cur, strip, j0, nr);
+        const uint32_t i = strip * VF_GM_QCOLS + lane;
+        const uint32_t nrows = min(nr + 1u, f.G - j0);      // vertex rows of this task
         const bool colv = i < f.G;
         const bool cellv = lane < VF_GM_QCOLS && i + 1u < f.G;
         // ---- per-column and per-row constants ----
@@ -272,7 +288,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az.coord, 1.1f)), 0.25f);
         }
         __syncwarp();
+        unsigned long long tp0 = 0ull, tp1 = 0ull, tp2 = 0ull;
+        if (dbg) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tp0) :: "memory"); tp0 += (wx != 12345.0f ? 0ull : 1ull); }
         if (TMA) { vf_mbar_wait(&w.mbar[stage], (parity >> stage) & 1u); parity ^= 1u << stage; }
+        if (dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tp1) :: "memory");
 
         int32_t pX = 0, pY = 0, pXn = 0, pYn = 0;          // previous row: own vertex and right neighbour
         float pZ = 0.0f, pZn = 0.0f;
@@ -398,26 +417,53 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         };
 
         row();                                              // row 0 primes the previous-row registers
+        if (dbg) {
+            tp2 = (unsigned long long)pX & 1ull;            // the stamp waits for the row's results
+            unsigned long long tq;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tq) :: "memory");
+            tp2 = tq + tp2 - ((unsigned long long)pX & 1ull);
+            if (lane == 0) {
+                unsigned long long* acc = dbg + 2u * gridDim.x * VF_GM_WARPS + ntasks + 4u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5));
+                acc[0] += tp0 - t_task; acc[1] += tp1 - tp0; acc[2] += tp2 - tp1; acc[3] += 1ull;
+            }
+        }
         bool fast = true;                                   // no vertex outside the guard band met in this task so far
-        while (r < nrows) {
-            if (fast) {
+        uint32_t asked = 0u, nxt = 0u;
 #pragma unroll 1
-                while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
-                    if (!row_pair()) { fast = false; break; }
-            }
-            if (!fast || r + 1u == nrows) {
+        for (uint32_t phase = 0u; phase < 3u; ++phase) {    // odd limits: row pairs stay aligned (r is odd here)
+            const uint32_t lim = phase == 2u ? nrows : min(nrows, ((nrows * (2u + phase)) >> 2) | 1u);
+            while (r < lim) {
+                if (fast) {
 #pragma unroll 1
-                while (r < nrows && q.qn <= VF_GM_QCAP - 32u) row();
+                    while (r + 1u < lim && q.qn <= VF_GM_QCAP - 32u)
+                        if (!row_pair()) { fast = false; break; }
+                }
+                if (!fast || r + 1u == lim) {
+#pragma unroll 1
+                    while (r < lim && q.qn <= VF_GM_QCAP - 32u) row();
+                }
+                __syncwarp();
+                if (q.qn >= 16u)
+                    q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), false, axis, dem, vis, big_prims, big_capacity, counters));
             }
-            __syncwarp();
-            if (q.qn >= 16u)
-                q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), false, axis, dem, vis, big_prims, big_capacity, counters));
+            if (phase == 0u) asked = ask_task();
+            else if (phase == 1u) { nxt = got_task(asked); issue(nxt, stage ^ 1u); }
         }
         __syncwarp();                                       // all reads of this stage and of the row tables are done
+        if (dbg) {                                          // profiling aid (VF_GM_DBG): duration of every task
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (lane == 0) dbg[2u * gridDim.x * VF_GM_WARPS + cur] = t1 - t_task;
+            t_task = t1;
+        }
         cur = nxt;
-        nxt = got_task(asked);
         stage ^= 1u;
     }
     q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), true, axis, dem, vis, big_prims, big_capacity, counters));
     vf_gm_drain_long<DEPTH>(f, w, q, true, lane, vis);
+    if (dbg) {
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (lane == 0) dbg[2u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5)) + 1u] = t1;
+    }
 }

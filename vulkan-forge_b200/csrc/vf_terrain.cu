@@ -45,6 +45,8 @@ struct vf_scene {
     uint32_t* d_counters = nullptr;      // = d_tile_count + n_tiles
     uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [2] high-water marks (pairs, queued prims)
     uint32_t* d_maxpairs = nullptr;      // = d_tile_off + n_tiles + 1
+    uint2* d_segtab = nullptr;           // k_geom_march row segments (first row, rows), rebuilt when G changes
+    uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
@@ -87,7 +89,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_dem); cudaFree(s->d_axis); cudaFree(s->d_lut); cudaFree(s->d_frame);
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
-    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag);
+    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag); cudaFree(s->d_segtab);
     cudaFree(s->d_dem_back);
     if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
@@ -446,15 +448,59 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     const uint32_t workers = (uint32_t)sm_count * per_sm * VF_GM_WARPS;
     uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
     rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
-    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
+    // Row segments: full height while plenty of work is left, then tapering (guided self-scheduling:
+    // a task is 1/(taper x workers) of what remains) so that the last tasks handed out are short.
+    static const int taper = getenv("VF_GM_TAPER") ? atoi(getenv("VF_GM_TAPER")) : 1;
+    static const int min_rows = getenv("VF_GM_MIN_ROWS") ? atoi(getenv("VF_GM_MIN_ROWS")) : 4;
+    if (s->segtab_G != s->G || s->segtab_workers != workers) {
+        std::vector<uint2> tab;
+        const uint32_t lo = std::min<uint32_t>(std::max(min_rows, 1), rows);
+        for (uint32_t j = 0; j < gm;) {
+            uint32_t h = rows;
+            if (taper > 0) h = (uint32_t)(((uint64_t)(gm - j) * nstrips) / ((uint64_t)taper * workers));
+            h = std::min(std::min(std::max(h, lo), rows), gm - j);
+            tab.push_back(make_uint2(j, h));
+            j += h;
+        }
+        if (tab.size() > s->segtab_cap) {
+            if (s->d_segtab) cudaFree(s->d_segtab);
+            s->d_segtab = nullptr; s->segtab_cap = 0;
+            VF_CUDA(cudaMalloc(&s->d_segtab, tab.size() * sizeof(uint2)));
+            s->segtab_cap = (uint32_t)tab.size();
+        }
+        VF_CUDA(cudaStreamSynchronize(s->stream));      // frames in flight may still read the old table
+        VF_CUDA(cudaMemcpy(s->d_segtab, tab.data(), tab.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+        s->segtab_n = (uint32_t)tab.size(); s->segtab_G = s->G; s->segtab_workers = workers;
+    }
+    const uint32_t nsegs = s->segtab_n, ntasks = nstrips * nsegs;
     const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * per_sm, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
+    // profiling aid: VF_GM_DBG=<file> dumps [ctas*8][start,end] ns + per-task ns of the last launch
+    static const char* dbg_path = getenv("VF_GM_DBG");
+    static unsigned long long* d_dbg = nullptr;
+    static size_t dbg_words = 0;
+    if (dbg_path) {
+        const size_t need = 6 * (size_t)ctas * VF_GM_WARPS + ntasks;
+        if (need > dbg_words) { if (d_dbg) cudaFree(d_dbg); VF_CUDA(cudaMalloc(&d_dbg, need * 8)); dbg_words = need; }
+        VF_CUDA(cudaMemsetAsync(d_dbg, 0, need * 8, s->stream));
+    }
 #define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
-        f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, rows)
+        f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, dbg_path ? d_dbg : nullptr)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
     else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }
 #undef VF_GM_LAUNCH2
 #undef VF_GM_LAUNCH
+    if (dbg_path) {
+        const size_t need = 6 * (size_t)ctas * VF_GM_WARPS + ntasks;
+        std::vector<unsigned long long> h(need + 4);
+        VF_CUDA(cudaStreamSynchronize(s->stream));
+        VF_CUDA(cudaMemcpy(h.data() + 4, d_dbg, need * 8, cudaMemcpyDeviceToHost));
+        h[0] = ctas * VF_GM_WARPS; h[1] = ntasks; h[2] = nstrips; h[3] = ((unsigned long long)nsegs << 32) | (rows << 8);
+        static int dump_no = 0;
+        char path[512];
+        snprintf(path, sizeof path, "%s.%d", dbg_path, dump_no++);
+        if (FILE* fp = fopen(path, "wb")) { fwrite(h.data(), 8, h.size(), fp); fclose(fp); }
+    }
     return VF_OK;
 }
 

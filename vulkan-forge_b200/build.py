@@ -47,6 +47,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
         cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "--fmad=false",
                "-std=c++17", "-ccbin", CXX, "-Xcompiler", "-fPIC,-ffp-contract=off",
                "-shared", "-o", out] + [os.path.join(CSRC, s) for s in CUDA_SRCS] + ["-lz"]
+        cmd[1:1] = os.environ.get("VF_NVCC_EXTRA", "").split()      # e.g. -DVF_GM_WARPS=6 -DVF_GM_CTAS=3 for tuning runs
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")

@@ -5,13 +5,12 @@
 //
 //   task     : 32 vertex columns x up to 25 vertex rows of the grid (31 x 24 cells); tasks are handed
 //              out in order by one atomic counter, every warp is its own worker.  The row segments
-//              get shorter towards the end of the grid (host-built table), and a worker asks for
-//              its next task only half way through the current one: both keep the finish times of
-//              the 2368 workers close together (measured with VF_GM_DBG + tools/gm_tasks.py)
+//              get shorter towards the end of the grid (host-built table), which keeps the finish
+//              times of the 2368 workers close together (VF_GM_DBG + tools/gm_tasks.py show them)
 //   staging  : the task's 25 x 32 DEM texels are one 2-D TMA box (cp.async.bulk.tensor, 36 texels
 //              wide: a box must start on a 16-byte boundary in global memory, strips start every
-//              31 columns) into the warp's private two-stage ring; the box of task n+1 is issued
-//              when three quarters of task n are done
+//              31 columns) into the warp's private two-stage ring; the box of task n+1 is in
+//              flight while task n runs
 //   march    : lane = vertex column.  The warp walks down the rows; a lane keeps the previous row's
 //              snapped vertex in registers and gets the right-hand neighbour by shuffle, so a cell
 //              costs one vertex stage + two shuffles + one bbox test.  Cells whose bbox holds no
@@ -26,7 +25,12 @@
 #include <type_traits>
 #include "vf_terrain_kernels.cuh"
 
+#ifndef VF_GM_WARPS
 #define VF_GM_WARPS 8                        // warps per CTA (each independent)
+#endif
+#ifndef VF_GM_CTAS
+#define VF_GM_CTAS 2                         // resident CTAs per SM the register budget is set for
+#endif
 #define VF_GM_QCOLS 31                       // cell columns per task (32 vertex columns)
 #define VF_GM_ROWS 24                        // cell rows per task
 #define VF_GM_BOX_X 36                       // TMA box width: 32 columns + up to 3 of alignment slack
@@ -208,13 +212,16 @@ __device__ __forceinline__ bool vf_span_has_centre(int32_t mn, int32_t mx) {
 // (k_axis_identity), the task's texels are one 25 x 36 box.  Otherwise texels are gathered through
 // the axis tables (one coalesced __ldg per row, issued one row ahead).
 template <bool TMA, bool DEPTH, bool SHIPPED>
-__global__ void __launch_bounds__(VF_GM_WARPS * 32, 2)
+__global__ void __launch_bounds__(VF_GM_WARPS * 32, VF_GM_CTAS)
 k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap dem_map,
              const VfAxis* __restrict__ axis, const float* __restrict__ dem,
              unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims, uint32_t big_capacity,
              uint32_t* __restrict__ counters, const uint2* __restrict__ segtab, uint32_t nsegs,
              unsigned long long* __restrict__ dbg) {
     extern __shared__ __align__(128) unsigned char vf_gm_smem[];
+#ifndef VF_GM_PROFILE                                       // the timing dump costs registers: only in -DVF_GM_PROFILE builds
+    dbg = nullptr;
+#endif
     const uint32_t lane = threadIdx.x & 31u;
     VfGmWarpT<DEPTH>& w = reinterpret_cast<VfGmWarpT<DEPTH>*>(vf_gm_smem)[threadIdx.x >> 5];
     const uint32_t gm = f.G - 1u;
@@ -231,10 +238,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     };
     const uint32_t below = (1u << lane) - 1u;
 
-    // The dispenser's answer takes an L2 round trip and the texels of a task another one: the next
-    // task is asked for half way through the current one and its TMA starts at three quarters.
-    // (Asking earlier hides no more latency and leaves every worker with one more task in hand when
-    // the dispenser runs dry, which is what spreads the finish times.)
+    // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
     auto ask_task = [&]() -> uint32_t { return lane == 0 ? atomicAdd(&counters[VF_CNT_TASK], 1u) : 0u; };
     auto got_task = [&](uint32_t t) -> uint32_t { return __shfl_sync(0xffffffffu, t, 0); };
     auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
@@ -257,6 +261,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
     uint32_t cur = got_task(ask_task());
     issue(cur, 0u);
+    uint32_t nxt = got_task(ask_task());
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
     float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
@@ -270,6 +275,8 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     unsigned long long t_task = 0ull;
     if (dbg) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_task)); if (lane == 0) dbg[2u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5))] = t_task; }
     while (cur < ntasks) {
+        issue(nxt, stage ^ 1u);
+        const uint32_t asked = ask_task();                  // becomes `nxt` at the end of this task
         uint32_t strip, j0, nr;
         decode(cur, strip, j0, nr);
         const uint32_t i = strip * VF_GM_QCOLS + lane;
@@ -428,26 +435,19 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             }
         }
         bool fast = true;                                   // no vertex outside the guard band met in this task so far
-        uint32_t asked = 0u, nxt = 0u;
+        while (r < nrows) {
+            if (fast) {
 #pragma unroll 1
-        for (uint32_t phase = 0u; phase < 3u; ++phase) {    // odd limits: row pairs stay aligned (r is odd here)
-            const uint32_t lim = phase == 2u ? nrows : min(nrows, ((nrows * (2u + phase)) >> 2) | 1u);
-            while (r < lim) {
-                if (fast) {
-#pragma unroll 1
-                    while (r + 1u < lim && q.qn <= VF_GM_QCAP - 32u)
-                        if (!row_pair()) { fast = false; break; }
-                }
-                if (!fast || r + 1u == lim) {
-#pragma unroll 1
-                    while (r < lim && q.qn <= VF_GM_QCAP - 32u) row();
-                }
-                __syncwarp();
-                if (q.qn >= 16u)
-                    q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), false, axis, dem, vis, big_prims, big_capacity, counters));
+                while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
+                    if (!row_pair()) { fast = false; break; }
             }
-            if (phase == 0u) asked = ask_task();
-            else if (phase == 1u) { nxt = got_task(asked); issue(nxt, stage ^ 1u); }
+            if (!fast || r + 1u == nrows) {
+#pragma unroll 1
+                while (r < nrows && q.qn <= VF_GM_QCAP - 32u) row();
+            }
+            __syncwarp();
+            if (q.qn >= 16u)
+                q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), false, axis, dem, vis, big_prims, big_capacity, counters));
         }
         __syncwarp();                                       // all reads of this stage and of the row tables are done
         if (dbg) {                                          // profiling aid (VF_GM_DBG): duration of every task
@@ -457,6 +457,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             t_task = t1;
         }
         cur = nxt;
+        nxt = got_task(asked);
         stage ^= 1u;
     }
     q.unpack(vf_gm_drain_cells<DEPTH>(f, w, q.pack(), true, axis, dem, vis, big_prims, big_capacity, counters));

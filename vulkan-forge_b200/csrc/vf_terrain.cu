@@ -444,7 +444,7 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     }
     const uint32_t gm = s->G - 1;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
-    const uint32_t per_sm = 2u;             // CTAs per SM (launch bounds of k_geom_march)
+    const uint32_t per_sm = VF_GM_CTAS;     // CTAs per SM (launch bounds of k_geom_march)
     const uint32_t workers = (uint32_t)sm_count * per_sm * VF_GM_WARPS;
     uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
     rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
@@ -474,8 +474,12 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     }
     const uint32_t nsegs = s->segtab_n, ntasks = nstrips * nsegs;
     const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * per_sm, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
-    // profiling aid: VF_GM_DBG=<file> dumps [ctas*8][start,end] ns + per-task ns of the last launch
+    // profiling aid (builds with VF_NVCC_EXTRA=-DVF_GM_PROFILE only): VF_GM_DBG=<file> dumps [ctas*8][start,end] ns + per-task ns of the last launch
+#ifdef VF_GM_PROFILE
     static const char* dbg_path = getenv("VF_GM_DBG");
+#else
+    static const char* dbg_path = nullptr;
+#endif
     static unsigned long long* d_dbg = nullptr;
     static size_t dbg_words = 0;
     if (dbg_path) {

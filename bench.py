@@ -178,6 +178,7 @@ def main():
     from vulkan_forge._synthetic import synthetic_dem
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    numa = vf.bind_host_to_gpu(local) if world > 1 and not os.environ.get("VF_NO_BIND") else {"bound": False}
     torch.cuda.set_device(local)
     if world > 1:
         import torch.distributed as dist
@@ -288,7 +289,7 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD,
-                       "frames_per_step_per_gpu": F, "l2": "flushed between steps (256 MiB write)", "sharding": "independent frames per GPU, no collective"},
+                       "frames_per_step_per_gpu": F, "l2": "flushed between steps (256 MiB write)", "sharding": "independent frames per GPU, no collective", "host_binding": numa},
             "mpix_per_s": fps * W * H / 1e6,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},

@@ -81,11 +81,11 @@ def grid_generate(nx: int, nz: int, spacing=(1.0, 1.0), origin="center"):
 
 generate_grid = grid_generate                # legacy alias (reference :172)
 
-from .orbit import orbit_cameras, render_orbit, shard_range  # noqa: E402  (additive multi-GPU helper)
+from .orbit import bind_host_to_gpu, orbit_cameras, render_orbit, shard_range  # noqa: E402  (additive multi-GPU helper)
 
 __all__ = [
     "Renderer", "TerrainSpike", "render_triangle_rgba", "render_triangle_png", "make_terrain",
     "colormap_supported", "camera_look_at", "camera_perspective", "camera_view_proj",
     "dem_stats", "dem_normalize", "grid_generate", "generate_grid", "__version__",
-    "Scene", "enumerate_adapters", "device_probe", "orbit_cameras", "render_orbit", "shard_range",
+    "Scene", "enumerate_adapters", "device_probe", "orbit_cameras", "render_orbit", "shard_range", "bind_host_to_gpu",
 ]

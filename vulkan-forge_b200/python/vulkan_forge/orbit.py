@@ -19,6 +19,35 @@ def shard_range(n_frames: int, rank: int, world: int):
     return (rank * n_frames) // world, ((rank + 1) * n_frames) // world
 
 
+def bind_host_to_gpu(local_index: int = 0) -> dict:
+    """Pins the calling process to the CPUs next to GPU `local_index` (as CUDA numbers it, i.e. after
+    CUDA_VISIBLE_DEVICES), so that pinned host buffers allocated afterwards land on the GPU's NUMA
+    node and the per-GPU DMA streams of a one-process-per-GPU job do not share one socket's memory.
+    Call it before the first CUDA allocation.  Returns what was done; never raises (a container may
+    hide the topology or restrict the CPU set)."""
+    info = {"bound": False}
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = [v.strip() for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
+        if local_index < len(vis) and not vis[local_index].isdigit():
+            h = pynvml.nvmlDeviceGetHandleByUUID(vis[local_index])
+        else:
+            h = pynvml.nvmlDeviceGetHandleByIndex(int(vis[local_index]) if local_index < len(vis) else local_index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        near = {64 * i + b for i, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        info.update(near=len(near), allowed=len(allowed))
+        both = near & allowed
+        if both and both != allowed:
+            os.sched_setaffinity(0, both)
+            info.update(bound=True, cpus=len(both))
+    except Exception as e:  # noqa: BLE001 - topology is a hint, never a requirement
+        info["error"] = f"{type(e).__name__}: {e}"
+    return info
+
+
 def orbit_cameras(n_frames: int, radius: float = 3.0 * math.sqrt(2.0), height: float = 2.0,
                   fovy_deg: float = 45.0, znear: float = 0.1, zfar: float = 100.0, start: int = 0,
                   stop: int | None = None):

@@ -171,3 +171,64 @@ def test_height_upload_roundtrip(vf, shape):                           # tests/t
         r.debug_read_height_patch(0, 1, 1, shape[0])
     with pytest.raises(RuntimeError, match="patch dimensions must be > 0"):
         r.debug_read_height_patch(0, 0, 0, 1)
+
+
+# ---- differential fuzzing (tools/fuzz_parity.py) ---------------------------------------------
+def _fuzz():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("vf_fuzz_parity", os.path.join(ROOT, "tools", "fuzz_parity.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+# Found by the fuzzer: grids of 530+ vertices a side give k_geom_march tasks of several rows; with a
+# camera close to (or inside) the terrain the first vertex row of a task can lie outside the guard
+# band, and the two-rows-at-a-time fast path used to continue from it without the clip state.
+_FUZZ_REGRESSIONS = [
+    dict(W=1, H=17, G=836, dw=835, dh=836, seed=1022241656, eye=(-0.20915687370489333, 1.3276651954749488, -0.1938512144016744),
+         tgt=(-0.20815687370489333, 0.0, -0.1938512144016744), fovy=90.0, znear=0.1, zfar=3.0, spacing=2.0, exag=2.0, mode=1, depth=0,
+         cmap="magma", lo=-0.5888416895866394, hi=0.5424208173751831),
+    dict(W=16, H=568, G=1063, dw=1062, dh=1063, seed=870961174, eye=(-0.2371148881262813, 0.7558845256859157, 0.14162109310250104),
+         tgt=(-0.9095650163295042, 0.0, -0.14357839549558027), fovy=90.0, znear=0.01, zfar=10.0, spacing=1.0, exag=2.0, mode=1, depth=1,
+         cmap="terrain", lo=-0.5365256199836731, hi=0.5347423086166382),
+    dict(W=36, H=29, G=817, dw=817, dh=817, seed=518997034, eye=(-0.06159753803867862, -2.076090922529322, 0.2585386545596223),
+         tgt=(-0.06059753803867862, 0.0, 0.2585386545596223), fovy=45.0, znear=0.5, zfar=3.0, spacing=1.0, exag=2.0, mode=0, depth=0,
+         cmap="terrain", lo=-0.5542551407814026, hi=0.501332772731781),
+    dict(W=355, H=33, G=670, dw=671, dh=670, seed=604203175, eye=(-0.20128530605246475, 1.628495349921721, -0.3871352855286505),
+         tgt=(-0.20028530605246475, 0.0, -0.3871352855286505), fovy=20.0, znear=0.01, zfar=100.0, spacing=0.5, exag=1.0, mode=1, depth=1,
+         cmap="viridis", lo=-0.5893525013923645, hi=0.5419024953842163),
+    dict(W=272, H=193, G=1019, dw=1019, dh=1019, seed=757362591, eye=(-0.21935821393244004, 0.4826241812021064, -0.028272396321713744),
+         tgt=(-0.08587378354637576, 0.0, 0.9006280450266455), fovy=90.0, znear=0.1, zfar=10.0, spacing=1.0, exag=2.0, mode=1, depth=0,
+         cmap="viridis", lo=-0.536085141658783, hi=0.5352432856559753),
+    dict(W=14, H=264, G=946, dw=88, dh=278, seed=931067945, eye=(0.265642581102838, 0.5883513195032288, 0.37803053320399993),
+         tgt=(0.3961539000131138, -0.3968453150433958, -0.6292692226925838), fovy=120.0, znear=0.01, zfar=3.0, spacing=0.5, exag=1.0, mode=0,
+         depth=0, cmap="viridis", lo=-0.5523202548027039, hi=0.5304822454452515),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", _FUZZ_REGRESSIONS, ids=lambda c: f"G{c['G']}_{c['W']}x{c['H']}_m{c['mode']}d{c['depth']}")
+def test_fuzz_regressions(case):
+    fz = _fuzz()
+    ok, detail, nothing = fz.check_case(case, fz.dem_for(case))
+    assert not nothing, "regression camera sees nothing"
+    assert ok, detail
+
+
+@pytest.mark.gpu
+def test_fuzz_short_run():
+    """20 s of seeded random frames (sizes, grids up to 2600, DEM shapes, cameras inside / grazing /
+    looking away, camera / sheared / orthographic matrices, both modes, depth on and off)."""
+    fz = _fuzz()
+    rng = np.random.default_rng(20240607)
+    import time
+    t0, n, bad = time.time(), 0, []
+    while time.time() - t0 < 20.0:
+        c, dem = fz.random_case(rng)
+        ok, detail, _ = fz.check_case(c, dem)
+        n += 1
+        if not ok:
+            bad.append((detail, c))
+    assert n >= 50, f"only {n} frames in 20 s"
+    assert not bad, f"{len(bad)} of {n} frames differ; first: {bad[0]}"

@@ -1,0 +1,160 @@
+"""Differential fuzzing of the terrain frame: CUDA path (through the C ABI) against the CPU oracle on
+random frame sizes, grids, DEM shapes, cameras (far, near, inside the terrain, grazing), modes and
+depth settings.  NORTHSTAR frames must be byte-identical; SHIPPED frames (sin/cos in the vertex and
+fragment stage) within 1 LSB on >= 99.9 % of the pixels.  Test infrastructure: run on the GPU box,
+  python tools/fuzz_parity.py [seconds] [seed]
+prints one line per mismatch (with everything needed to replay it) and a summary; exit code 1 on
+any mismatch."""
+import ctypes as C
+import json
+import math
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "vulkan-forge_b200", "python"))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import numpy as np
+import vf_oracle as o
+import vulkan_forge as vf
+from vulkan_forge._synthetic import synthetic_dem
+
+lib = C.CDLL(os.path.join(ROOT, "vulkan-forge_b200", "python", "vulkan_forge", "libvfcuda.so"))
+lib.vf_last_error.restype = C.c_char_p
+LUTS = {n: np.fromfile(os.path.join(ROOT, "tests", "golden", f"lut_{n}.rgba"), np.uint8) for n in ("viridis", "magma", "terrain")}
+CMAP_ID = {"viridis": 0, "magma": 1, "terrain": 2}
+
+
+def ptr(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def gpu_frame(W, H, G, cmap, dem, u, mode, depth, lo, hi):
+    scene = C.c_void_p()
+    assert lib.vf_scene_create(W, H, G, CMAP_ID[cmap], 0, C.byref(scene)) == 0, lib.vf_last_error()
+    try:
+        if dem is not None:
+            assert lib.vf_scene_set_height_f32(scene, ptr(dem, C.c_float), dem.shape[1], dem.shape[0]) == 0, lib.vf_last_error()
+        assert lib.vf_scene_set_uniforms(scene, ptr(u, C.c_float)) == 0
+        assert lib.vf_scene_set_mode(scene, mode, depth, C.c_float(lo), C.c_float(hi)) == 0
+        out = np.zeros((H, W, 4), np.uint8)
+        assert lib.vf_scene_render_rgba(scene, ptr(out, C.c_uint8)) == 0, lib.vf_last_error()
+        out2 = np.zeros((H, W, 4), np.uint8)       # second frame: the self-cleaning visibility buffer must be clean
+        assert lib.vf_scene_render_rgba(scene, ptr(out2, C.c_uint8)) == 0, lib.vf_last_error()
+        assert np.array_equal(out, out2), "second frame of the same scene differs from the first"
+        return out
+    finally:
+        lib.vf_scene_destroy(scene)
+
+
+def dem_for(c, rng=None):
+    """The DEM of a recorded case: everything but the optional spikes / flattening is a function of the case."""
+    base = synthetic_dem(c["seed"] % 7, max(c["dw"], c["dh"]))[:c["dh"], :c["dw"]]
+    return np.ascontiguousarray(base * np.float32(c.get("scale", 1.0)))
+
+
+def check_case(c, dem, threads=0):
+    u = np.ascontiguousarray(uniforms_for(c), np.float32)
+    if c.get("matrix") == "sheared":
+        u[16 + 4] = np.float32(0.15); u[16 + 1] = np.float32(-0.05)
+    elif c.get("matrix") == "ortho":
+        P = np.zeros(16, np.float32)
+        P[0], P[5], P[10], P[14], P[15] = 0.45, 0.6, -1.0 / 20.0, 0.0, 1.0
+        u[16:32] = P
+    ref = o.render_terrain(c["W"], c["H"], c["G"], dem, u, LUTS[c["cmap"]], mode=o.MODE_NORTHSTAR if c["mode"] else o.MODE_SHIPPED,
+                           depth=bool(c["depth"]), h_min=c["lo"], h_max=c["hi"], threads=threads)
+    got = gpu_frame(c["W"], c["H"], c["G"], c["cmap"], dem, u, c["mode"], c["depth"], c["lo"], c["hi"])
+    empty = not (ref[..., :3] != ref[0, 0, :3]).any()
+    if c["mode"] == 1:
+        return np.array_equal(got, ref), f"{int((got != ref).any(-1).sum())} pixels differ", empty
+    d = np.abs(got.astype(np.int16) - ref.astype(np.int16)).max(-1)
+    ok = (d <= 1).mean() >= 0.999 if d.size >= 1000 else (d <= 1).sum() >= d.size - 1
+    return bool(ok), f"within 1 LSB {float((d <= 1).mean()):.5f}, max {int(d.max())}", empty
+
+
+def random_case(rng):
+    W = int(rng.choice([rng.integers(1, 40), rng.integers(40, 400), rng.integers(400, 900)]))
+    H = int(rng.choice([rng.integers(1, 40), rng.integers(40, 300), rng.integers(300, 700)]))
+    G = int(rng.choice([rng.integers(2, 8), rng.integers(8, 70), rng.integers(70, 400), rng.integers(400, 1100), rng.integers(1100, 2600)]))
+    kind = rng.integers(0, 4)
+    if kind == 0:
+        dw, dh = G, G                                   # identity mapping: TMA path when the pitch allows
+    elif kind == 1:
+        dw, dh = int(rng.integers(1, 300)), int(rng.integers(1, 300))
+    elif kind == 2:
+        dw, dh = G + int(rng.integers(-1, 2)), G
+        dw = max(dw, 1)
+    else:
+        dw, dh = int(rng.integers(2, 1200)), int(rng.integers(2, 1200))
+    seed = int(rng.integers(0, 1 << 30))
+    scale = float(rng.choice([0.2, 1.0, 3.0]))
+    dem = dem_for(dict(seed=seed, dw=dw, dh=dh, scale=scale))
+    if rng.random() < 0.3:                               # spikes: needles, huge triangles
+        k = int(rng.integers(1, 12))
+        dem[rng.integers(0, dh, k), rng.integers(0, dw, k)] += rng.normal(0, 3.0, k).astype(np.float32)
+    if rng.random() < 0.1:
+        dem[:] = np.float32(rng.normal())                # flat
+    style = rng.integers(0, 6)
+    if style == 0:      # orbit-like
+        a = rng.uniform(0, 2 * math.pi); r = rng.uniform(1.5, 8.0)
+        eye = (r * math.cos(a), rng.uniform(0.3, 4.0), r * math.sin(a)); tgt = (0.0, 0.0, 0.0)
+    elif style == 1:    # inside / just above the terrain: near-plane clipping
+        eye = (rng.uniform(-1, 1), rng.uniform(-0.2, 0.6), rng.uniform(-1, 1)); tgt = (rng.uniform(-2, 2), rng.uniform(-0.5, 0.5), rng.uniform(-2, 2))
+    elif style == 2:    # straight down / up
+        eye = (rng.uniform(-0.5, 0.5), rng.uniform(1.0, 6.0) * rng.choice([-1, 1]), rng.uniform(-0.5, 0.5)); tgt = (eye[0] + 1e-3, 0.0, eye[2])
+    elif style == 3:    # grazing
+        eye = (rng.uniform(2, 6), rng.uniform(0.0, 0.15), rng.uniform(-1, 1)); tgt = (0.0, 0.05, 0.0)
+    elif style == 4:    # looking away: (almost) nothing visible
+        eye = (3.0, 2.0, 3.0); tgt = (6.0, 3.0, 6.0 + rng.uniform(-1, 1))
+    else:               # close-up: big triangles (binned path)
+        eye = (rng.uniform(-0.3, 0.3), rng.uniform(0.2, 0.8), rng.uniform(-0.3, 0.3)); tgt = (eye[0] + rng.uniform(-1, 1), 0.0, eye[2] + rng.uniform(-1, 1))
+    fovy = float(rng.choice([20.0, 45.0, 90.0, 120.0]))
+    znear = float(rng.choice([0.01, 0.1, 0.5])); zfar = float(rng.choice([10.0, 100.0, 3.0]))
+    spacing = float(rng.choice([1.0, 1.0, 0.5, 2.0])); exag = float(rng.choice([1.0, 1.0, 2.0, 0.25]))
+    mode = int(rng.integers(0, 2)); depth = int(rng.integers(0, 2))
+    cmap = str(rng.choice(["viridis", "magma", "terrain"]))
+    matrix = str(rng.choice(["camera"] * 6 + ["sheared", "ortho"]))
+    lo = float(np.percentile(dem, 1)) - 1e-3; hi = float(np.percentile(dem, 99)) + 1e-3
+    return dict(W=W, H=H, G=G, dw=dw, dh=dh, seed=seed, eye=tuple(map(float, eye)), tgt=tuple(map(float, tgt)), fovy=fovy,
+                znear=znear, zfar=zfar, spacing=spacing, exag=exag, mode=mode, depth=depth, cmap=cmap, lo=lo, hi=hi,
+                style=int(style), scale=scale, matrix=matrix), dem
+
+
+def uniforms_for(c):
+    kw = {}
+    try:
+        return o.look_at_uniforms(c["W"], c["H"], c["eye"], c["tgt"], (0, 1, 0), c["fovy"], c["znear"], c["zfar"],
+                                  spacing=c["spacing"], exaggeration=c["exag"], **kw)
+    except TypeError:
+        return o.look_at_uniforms(c["W"], c["H"], c["eye"], c["tgt"], (0, 1, 0), c["fovy"], c["znear"], c["zfar"])
+
+
+def main():
+    budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
+    seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    rng = np.random.default_rng(seed)
+    threads = len(os.sched_getaffinity(0))
+    t0 = time.time(); n = 0; bad = 0; empty = 0; stats = {}
+    while time.time() - t0 < budget:
+        c, dem = random_case(rng)
+        try:
+            ok, detail, nothing = check_case(c, dem, threads)
+        except AssertionError as e:
+            bad += 1
+            print("ERROR", e, json.dumps(c), flush=True)
+            continue
+        n += 1
+        empty += int(nothing)
+        key = (c["style"], c["mode"], c["depth"])
+        stats[key] = stats.get(key, 0) + 1
+        if not ok:
+            bad += 1
+            print("MISMATCH", detail, json.dumps(c), flush=True)
+    print(f"fuzz: {n} frames in {time.time() - t0:.0f} s, {bad} mismatches, {empty} frames saw nothing, seed {seed}")
+    print("cases per (camera style, mode, depth):", sorted(stats.items()))
+    sys.exit(1 if bad else 0)
+
+
+if __name__ == "__main__":
+    main()

@@ -436,14 +436,19 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         }
         bool fast = true;                                   // no vertex outside the guard band met in this task so far
         while (r < nrows) {
-            if (fast) {
+            // row_pair assumes a clean previous row (it neither reads nor writes the clip state):
+            // after a row with a vertex outside the guard band the general routine runs until a
+            // row is clean again (pnin == 0 implies pst == pstn == 0)
+            if (fast && pnin == 0u && r + 1u < nrows) {
 #pragma unroll 1
                 while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
                     if (!row_pair()) { fast = false; break; }
-            }
-            if (!fast || r + 1u == nrows) {
+            } else {
 #pragma unroll 1
-                while (r < nrows && q.qn <= VF_GM_QCAP - 32u) row();
+                while (r < nrows && q.qn <= VF_GM_QCAP - 32u) {
+                    row();
+                    if (fast && pnin == 0u && r + 1u < nrows) break;
+                }
             }
             __syncwarp();
             if (q.qn >= 16u)

@@ -85,6 +85,20 @@ def test_dem_percentile_ties_zeros_and_outliers(ext, oracle):
     assert ext.dem_minmax(c, True) == (-7.25, -7.25)
 
 
+def test_dem_minmax_sign_of_zero_extremes(ext, oracle):
+    """`if v < lo { lo = v }` keeps the first element equal to the extreme and -0 == +0, so a zero
+    extreme carries the sign of the first zero of the slice (found by tools/fuzz_parity.py dem)."""
+    for first, n in ((-0.0, 81), (0.0, 81), (-0.0, 1_538_639), (0.0, 3)):
+        z = np.where(np.arange(n) % 2 == 0, np.float32(first), np.float32(-first)).astype(np.float32)
+        lo, hi = ext.dem_minmax(z, False)
+        olo, ohi = oracle.min_max(z, False)
+        assert np.float32(lo).tobytes() == olo.tobytes() and np.float32(hi).tobytes() == ohi.tobytes(), (first, n)
+    a = np.array([3.0, 0.0, -0.0, 5.0], np.float32)          # min is +0 (first zero), max is 5
+    assert np.float32(ext.dem_minmax(a, False)[0]).tobytes() == np.float32(0.0).tobytes()
+    b = np.array([-3.0, -0.0, 0.0, -5.0], np.float32)        # max is -0 (first zero)
+    assert np.float32(ext.dem_minmax(b, False)[1]).tobytes() == np.float32(-0.0).tobytes()
+
+
 def test_renderer_terrain_stats_and_range(vf, oracle):                 # tests/test_height_upload.py:20-49
     r = vf.Renderer(32, 32)
     with pytest.raises(RuntimeError, match=r"no terrain uploaded; call add_terrain\(\) first"):

@@ -130,7 +130,55 @@ def uniforms_for(c):
         return o.look_at_uniforms(c["W"], c["H"], c["eye"], c["tgt"], (0, 1, 0), c["fovy"], c["znear"], c["zfar"])
 
 
+def random_dem_values(rng):
+    """Arrays that stress the exact percentile select: ties, signed zeros, denormals, infinities,
+    huge dynamic range, constant data, sizes around the radix-select pass boundaries."""
+    n = int(rng.choice([rng.integers(1, 5), rng.integers(5, 300), rng.integers(300, 70000), rng.integers(70000, 3000000)]))
+    kind = int(rng.integers(0, 8))
+    if kind == 0:
+        a = rng.normal(0, 1, n)
+    elif kind == 1:
+        a = rng.integers(-3, 4, n).astype(np.float64)                    # heavy ties
+    elif kind == 2:
+        a = np.where(rng.random(n) < 0.5, 0.0, -0.0)                     # signed zeros only
+    elif kind == 3:
+        a = rng.normal(0, 1, n) * 10.0 ** rng.integers(-40, 38, n)       # denormals .. near overflow
+    elif kind == 4:
+        a = np.full(n, rng.normal())
+    elif kind == 5:
+        a = rng.normal(0, 1, n); a[rng.integers(0, n, max(1, n // 50))] = rng.choice([np.inf, -np.inf, 1e30, -1e30])
+    elif kind == 6:
+        a = np.sort(rng.normal(0, 1, n))[:: int(rng.choice([1, -1]))]
+    else:
+        a = rng.integers(0, 2, n) * 1e-45 + rng.integers(0, 2, n) * -1e-45   # +-smallest denormal and zeros
+    with np.errstate(over="ignore"):
+        return np.ascontiguousarray(a, np.float32), kind
+
+
+def fuzz_dem(budget, seed):
+    """dem_minmax (min/max and the 1-99 % percentile pair of src/terrain_stats.rs:11-35) bit-for-bit."""
+    ext = vf._vulkan_forge
+    rng = np.random.default_rng(seed)
+    t0 = time.time(); n = 0; bad = 0
+    while time.time() - t0 < budget:
+        a, kind = random_dem_values(rng)
+        shape = (1, a.size) if rng.random() < 0.5 or a.size < 4 else (2, a.size // 2)
+        a = a[:shape[0] * shape[1]].reshape(shape)
+        for clamp in (False, True):
+            got = ext.dem_minmax(a, clamp)
+            ref = o.min_max(a, clamp)
+            same = all(np.float32(g).tobytes() == np.float32(r).tobytes() for g, r in zip(got, ref))
+            n += 1
+            if not same:
+                bad += 1
+                print("DEM MISMATCH", dict(kind=kind, n=int(a.size), clamp=clamp, got=[float(x) for x in got], ref=[float(x) for x in ref], seed=seed), flush=True)
+    print(f"fuzz dem: {n} calls in {time.time() - t0:.0f} s, {bad} mismatches, seed {seed}")
+    return bad
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "dem":
+        sys.exit(1 if fuzz_dem(float(sys.argv[2]) if len(sys.argv) > 2 else 30.0, int(sys.argv[3]) if len(sys.argv) > 3 else 1) else 0)
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0
     seed = int(sys.argv[2]) if len(sys.argv) > 2 else 1
     rng = np.random.default_rng(seed)

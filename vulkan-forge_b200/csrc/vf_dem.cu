@@ -132,6 +132,44 @@ k_dem_reduce(const float* __restrict__ data, uint32_t w, uint32_t h, uint32_t pi
     }
 }
 
+// index of the first +-0 of the image.  `if v < lo { lo = v }` (terrain_stats.rs:17, lib.rs:914) keeps
+// the FIRST element that equals the extreme value, and -0 == +0: when an extreme is zero its sign is
+// the sign of the first zero in index order, which an order-free reduction cannot know.
+__global__ void __launch_bounds__(256)
+k_dem_first_zero(const float* __restrict__ data, uint32_t w, uint32_t h, uint32_t pitch, unsigned long long* __restrict__ first) {
+    const size_t n = (size_t)w * h;
+    unsigned long long best = ~0ull;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = idx / w, c = idx - r * w;
+        if (__ldg(data + r * pitch + c) == 0.0f) { best = idx; break; }      // a thread's indices ascend
+    }
+    if (best != ~0ull) atomicMin(first, best);
+}
+
+// replaces a zero extreme by the first zero of the image (sign included); out2 = (lo, hi)
+static int fix_zero_sign(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, float out2[2], cudaStream_t stream) {
+    if (out2[0] != 0.0f && out2[1] != 0.0f) return VF_OK;
+    unsigned long long* d_first = nullptr;
+    VF_CUDA(cudaMalloc(&d_first, 8));
+    unsigned long long first = ~0ull;
+    cudaError_t e = cudaMemcpyAsync(d_first, &first, 8, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) {
+        const size_t n = (size_t)w * h;
+        const size_t blocks = (n + 255) / 256;
+        k_dem_first_zero<<<(int)(blocks > 148 * 16 ? 148 * 16 : blocks), 256, 0, stream>>>(d_data, w, h, pitch, d_first);
+        e = cudaMemcpyAsync(&first, d_first, 8, cudaMemcpyDeviceToHost, stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    float z = 0.0f;
+    if (e == cudaSuccess && first != ~0ull)
+        e = cudaMemcpy(&z, d_data + (size_t)(first / w) * pitch + (size_t)(first % w), 4, cudaMemcpyDeviceToHost);
+    cudaFree(d_first);
+    VF_CUDA(e);
+    if (out2[0] == 0.0f) out2[0] = z;
+    if (out2[1] == 0.0f) out2[1] = z;
+    return VF_OK;
+}
+
 __global__ void k_dem_keys_to_float(const uint32_t* __restrict__ acc, float* __restrict__ out2) {
     out2[0] = vf_key_float(acc[0]);
     out2[1] = vf_key_float(acc[1]);
@@ -182,6 +220,8 @@ int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t p
         k_dem_keys_to_float<<<1, 1, 0, stream>>>(acc, o2);
         VF_CUDA(cudaMemcpyAsync(out, o2, 8, cudaMemcpyDeviceToHost, stream));
         VF_CUDA(cudaStreamSynchronize(stream));
+        const int rc = fix_zero_sign(d_data, w, h, pitch, out, stream);
+        if (rc) return rc;
     } else {
         const size_t SAMPLE = 65536;
         size_t step = 1, m = n;
@@ -239,6 +279,8 @@ static int stats_device(const float* d_data, uint32_t w, uint32_t h, uint32_t pi
     VF_CUDA(cudaGetLastError());
     auto kf = [](uint32_t k) { uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; float f; memcpy(&f, &b, 4); return f; };
     out4[0] = kf(hk[0]); out4[1] = kf(hk[1]);
+    const int rcz = fix_zero_sign(d_data, w, h, pitch, out4, 0);
+    if (rcz) return rcz;
     out4[2] = (float)mean;
     out4[3] = (float)sqrt(hd[1] / (double)n);
     return VF_OK;

@@ -9,7 +9,7 @@
 #include <vector>
 
 #include "vf_internal.h"
-#include "vf_geom_split.cuh"
+#include "vf_geom_march.cuh"
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
 typedef CUresult (*vf_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -50,16 +50,13 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
-    VfCellQ cellq = {nullptr, nullptr, nullptr, 0};       // k_geom_cull -> k_cells
-    VfNeedleQ needleq = {nullptr, nullptr, nullptr, 0};   // k_cells -> k_needles
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
-    alignas(64) CUtensorMap dem_map_gc;  // same tensor, box 36x17 floats (k_geom_cull)
     alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
     bool use_tma = false;                // grid == DEM with identity texel mapping
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
     // front image render; swapped in by the next submit
     float* d_dem_back = nullptr;
-    alignas(64) CUtensorMap dem_map_b, dem_map_gm_b, dem_map_gc_b;
+    alignas(64) CUtensorMap dem_map_b, dem_map_gm_b;
     bool back_valid = false, back_pending = false, front_released_once = false;
     cudaStream_t upload_stream = nullptr;
     cudaEvent_t ev_uploaded = nullptr, ev_front_released = nullptr;
@@ -95,8 +92,6 @@ static void scene_free(vf_scene* s) {
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
     if (s->ev_front_released) cudaEventDestroy(s->ev_front_released);
     for (auto& t : s->tickets) if (t.done) cudaEventDestroy(t.done);
-    cudaFree(s->cellq.id); cudaFree(s->cellq.xy); cudaFree(s->cellq.z);
-    cudaFree(s->needleq.prim); cudaFree(s->needleq.xy); cudaFree(s->needleq.z);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -114,18 +109,6 @@ static int scene_alloc_pairs(vf_scene* s, uint32_t capacity) {
     VF_CUDA(cudaMalloc(&s->d_pair_prim, (size_t)capacity * 4));
     VF_CUDA(cudaMalloc(&s->d_sorted, (size_t)capacity * 4));
     s->capacity = capacity;
-    return VF_OK;
-}
-
-// structure-of-arrays queue: ids, `planes` int32 planes of coordinates, planes / 2 float planes of z
-template <typename Q>
-static int scene_alloc_queue(Q* q, uint32_t** ids, int planes, uint32_t capacity) {
-    cudaFree(*ids); cudaFree(q->xy); cudaFree(q->z);
-    *ids = nullptr; q->xy = nullptr; q->z = nullptr; q->cap = 0;
-    VF_CUDA(cudaMalloc(ids, (size_t)capacity * 4));
-    VF_CUDA(cudaMalloc(&q->xy, (size_t)capacity * 4 * planes));
-    VF_CUDA(cudaMalloc(&q->z, (size_t)capacity * 4 * (planes / 2)));
-    q->cap = capacity;
     return VF_OK;
 }
 
@@ -168,17 +151,16 @@ static int scene_rebuild_axis(vf_scene* s) {
     return VF_OK;
 }
 
-// the three 2-D tiled maps over a DEM image: boxes of k_geom (36x33), k_geom_march (36x25), k_geom_cull (36x17)
-static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pitch, CUtensorMap* m_tiled, CUtensorMap* m_march,
-                              CUtensorMap* m_cull) {
+// the two 2-D tiled maps over a DEM image: boxes of k_geom (36x33) and of k_geom_march (36x25)
+static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pitch, CUtensorMap* m_tiled, CUtensorMap* m_march) {
     if (!tmap_encoder()) return false;
     const cuuint64_t gdim[2] = {w, h};
     const cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4};
     const cuuint32_t estr[2] = {1, 1};
-    const cuuint32_t boxes[3][2] = {{VF_TMA_BOX_X, VF_TMA_BOX_Y}, {VF_GM_BOX_X, VF_GM_VROWS}, {VF_GM_BOX_X, VF_GC_VROWS}};
-    CUtensorMap* maps[3] = {m_tiled, m_march, m_cull};
+    const cuuint32_t boxes[2][2] = {{VF_TMA_BOX_X, VF_TMA_BOX_Y}, {VF_GM_BOX_X, VF_GM_VROWS}};
+    CUtensorMap* maps[2] = {m_tiled, m_march};
     bool ok = true;
-    for (int k = 0; k < 3; ++k)
+    for (int k = 0; k < 2; ++k)
         ok = ok && tmap_encoder()(maps[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, d_dem, gdim, gstride, boxes[k], estr,
                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -206,7 +188,6 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     s->use_tma = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
     memset(&s->dem_map_gm, 0, sizeof s->dem_map_gm);
-    memset(&s->dem_map_gc, 0, sizeof s->dem_map_gc);
     if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
         if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
         const uint32_t one = 1u;
@@ -216,7 +197,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
         VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (flag == 1u) {
-            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, &s->dem_map_gm, &s->dem_map_gc);
+            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, &s->dem_map_gm);
         }
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
@@ -269,11 +250,6 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>(cap, 1u << 30));
     if (rc) { scene_free(s); return rc; }
     rc = scene_alloc_big(s, 1u << 20);
-    if (rc) { scene_free(s); return rc; }
-    const uint64_t cells = (uint64_t)(grid - 1) * (grid - 1);
-    rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, (uint32_t)std::min<uint64_t>(cells + 32, 1u << 21));
-    if (rc) { scene_free(s); return rc; }
-    rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, (uint32_t)std::min<uint64_t>(2 * cells + 32, 1u << 20));
     if (rc) { scene_free(s); return rc; }
     if (cudaMalloc(&s->d_visbuf, (size_t)w * h * 8) != cudaSuccess) {
         scene_free(s);
@@ -375,55 +351,6 @@ static uint32_t clear_rgba8() {
     auto enc = [&](float x) { uint32_t c = 0; for (int k = 1; k < 256; ++k) if (thr[k] <= x) c = k; return c; };
     // clear colour (0.02, 0.02, 0.03, 1): src/scene/mod.rs:286
     return enc(0.02f) | (enc(0.02f) << 8) | (enc(0.03f) << 16) | 0xff000000u;
-}
-
-// k_geom_cull -> k_cells -> k_needles (vf_geom_split.cuh).  Rows per task shrink on coarse grids so
-// that every warp of the machine gets a few tasks.
-template <bool T, bool D, bool S>
-static int launch_cull(vf_scene* s, const VfFrame& f, int sm_count) {
-    static int per_sm = 0;
-    const size_t smem = VF_GC_WARPS * sizeof(VfGcWarpT<D>);
-    if (!per_sm) {
-        VF_CUDA(cudaFuncSetAttribute(k_geom_cull<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_geom_cull<T, D, S>, VF_GC_WARPS * 32, smem));
-        per_sm = std::max(per_sm, 1);
-    }
-    const uint32_t gm = s->G - 1;
-    const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
-    const uint32_t workers = (uint32_t)sm_count * (uint32_t)per_sm * VF_GC_WARPS;
-    uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
-    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GC_ROWS);
-    const uint32_t ntasks = nstrips * ((gm + rows - 1) / rows);
-    const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * (uint32_t)per_sm, (ntasks + VF_GC_WARPS - 1) / VF_GC_WARPS);
-    k_geom_cull<T, D, S><<<ctas, VF_GC_WARPS * 32, smem, s->stream>>>(f, s->dem_map_gc, s->d_axis, s->d_dem, s->cellq, s->d_counters, rows);
-    return VF_OK;
-}
-
-static int launch_geom_split(vf_scene* s, const VfFrame& f) {
-    static int sm_count = 0;
-    if (!sm_count) {
-        int dev = 0;
-        VF_CUDA(cudaGetDevice(&dev));
-        VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-    }
-    const bool shipped = f.mode == VF_MODE_SHIPPED;
-    int rc;
-#define VF_GC_PICK(T, D) (shipped ? launch_cull<T, D, true>(s, f, sm_count) : launch_cull<T, D, false>(s, f, sm_count))
-    if (s->use_tma) rc = f.depth ? VF_GC_PICK(true, true) : VF_GC_PICK(true, false);
-    else            rc = f.depth ? VF_GC_PICK(false, true) : VF_GC_PICK(false, false);
-#undef VF_GC_PICK
-    if (rc) return rc;
-    const uint32_t g2 = (uint32_t)sm_count * 8u;
-    if (f.depth) {
-        k_cells<true><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->cellq, s->d_visbuf, s->needleq, s->d_big,
-                                                 s->big_capacity, s->d_counters, s->d_maxpairs);
-        k_needles<true><<<g2, 256, 0, s->stream>>>(f, s->needleq, s->d_visbuf, s->d_counters, s->d_maxpairs);
-    } else {
-        k_cells<false><<<g2, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->cellq, s->d_visbuf, s->needleq, s->d_big,
-                                                  s->big_capacity, s->d_counters, s->d_maxpairs);
-        k_needles<false><<<g2, 256, 0, s->stream>>>(f, s->needleq, s->d_visbuf, s->d_counters, s->d_maxpairs);
-    }
-    return VF_OK;
 }
 
 // k_geom_march: persistent grid of warp workers; rows per task shrink on coarse grids so that every
@@ -530,7 +457,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
             k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
                 f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     } else {
-        int rc = getenv("VF_GEOM_SPLIT") ? launch_geom_split(s, f) : launch_geom_march(s, f);   // A/B switch
+        int rc = launch_geom_march(s, f);
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
@@ -580,7 +507,7 @@ static int scene_apply_pending_dem(vf_scene* s) {
     VF_CUDA(cudaEventRecord(s->ev_front_released, s->stream));   // every frame of the old image precedes this
     s->front_released_once = true;
     std::swap(s->d_dem, s->d_dem_back);
-    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b); std::swap(s->dem_map_gc, s->dem_map_gc_b);
+    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b);
     s->back_pending = false;
     return VF_OK;
 }
@@ -617,8 +544,8 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 // grown (the batch must be rendered again), < 0 = error code
 static int scene_check_overflow(vf_scene* s, int hslot) {
     const uint32_t* h = s->h_counters + (size_t)hslot * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
-    const uint32_t need = h[0], need_big = h[1], need_cells = h[2], need_needles = h[3];
-    if (need <= s->capacity && need_big <= s->big_capacity && need_cells <= s->cellq.cap && need_needles <= s->needleq.cap) return 0;
+    const uint32_t need = h[0], need_big = h[1];
+    if (need <= s->capacity && need_big <= s->big_capacity) return 0;
     VF_CUDA(cudaStreamSynchronize(s->stream));           // nothing in flight may still use the buffers
     if (need > (1u << 30)) return -vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
     int rc;
@@ -628,14 +555,6 @@ static int scene_check_overflow(vf_scene* s, int hslot) {
     }
     if (need_big > s->big_capacity) {
         rc = scene_alloc_big(s, need_big + need_big / 4 + 1024);
-        if (rc) return -rc;
-    }
-    if (need_cells > s->cellq.cap) {
-        rc = scene_alloc_queue(&s->cellq, &s->cellq.id, 8, need_cells + need_cells / 4 + 1024);
-        if (rc) return -rc;
-    }
-    if (need_needles > s->needleq.cap) {
-        rc = scene_alloc_queue(&s->needleq, &s->needleq.prim, 6, need_needles + need_needles / 4 + 1024);
         if (rc) return -rc;
     }
     return 1;
@@ -676,7 +595,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
         s->back_valid = false;
     }
     if (!s->back_valid) {
-        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, &s->dem_map_gm_b, &s->dem_map_gc_b))
+        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, &s->dem_map_gm_b))
             return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
         s->back_valid = true;
     }

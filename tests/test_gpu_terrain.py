@@ -194,6 +194,56 @@ def test_pair_buffer_growth(ext, oracle, luts):
     assert np.array_equal(got, ref)
 
 
+def test_queue_and_pair_buffers_grow_sync_and_async(ext, oracle, luts, synthetic_dem, monkeypatch):
+    """VF_TEST_SMALL_BUFFERS starts a scene with 4 queue slots and 256 pairs: a close-up overflows
+    both, the frame (or the whole pipelined batch) is rendered again after the buffers have grown,
+    and the result is the oracle's.  Covers scene_check_overflow on the synchronous and the ticket path."""
+    monkeypatch.setenv("VF_TEST_SMALL_BUFFERS", "1")
+    W, H, G = 400, 320, 12                                              # 242 triangles of thousands of pixels each
+    dem = synthetic_dem(9, G)
+    cams = [((0.1, 0.35, 0.1), (0.8, 0.0, 0.6), (0, 1, 0), 70.0, 0.01, 50.0),
+            ((3.0, 2.0, 3.0), (0, 0, 0), (0, 1, 0), 45.0, 0.1, 100.0),
+            ((-0.2, 0.25, 0.3), (-1.0, 0.0, -0.4), (0, 1, 0), 90.0, 0.01, 50.0)]
+    for depth in (False, True):
+        sc = ext.Scene(W, H, grid=G, colormap="magma")
+        sc.set_height_from_r32f(dem); sc.set_shading("northstar", depth=depth); sc.set_height_range(-0.3, 0.4)
+        want = []
+        for c in cams:
+            sc.set_camera_look_at(*c)
+            ref = oracle.render_terrain(W, H, G, dem, sc.debug_uniforms_f32(), luts["magma"], mode=oracle.MODE_NORTHSTAR,
+                                        depth=depth, h_min=-0.3, h_max=0.4)
+            want.append(ref)
+        sc.set_camera_look_at(*cams[0])
+        assert np.array_equal(sc.render_rgba(), want[0])                 # synchronous: grow + retry
+        m = sc.render_metrics()
+        assert m["bin_capacity"] > 256 and m["big_prims"] > 4 and m["bin_pairs"] <= m["bin_capacity"], m
+        sc2 = ext.Scene(W, H, grid=G, colormap="magma")                 # fresh tiny buffers, pipelined path
+        sc2.set_shading("northstar", depth=depth); sc2.set_height_range(-0.3, 0.4)
+        sc2.set_height_from_r32f_async(dem)
+        t1 = sc2.render_batch_rgba_async(cams)
+        t2 = sc2.render_batch_rgba_async(cams[::-1])                    # submitted with the tiny buffers too
+        a, b = sc2.collect(t1), sc2.collect(t2)                         # t1 grows them; t2 must still notice it overflowed
+        for k in range(3):
+            assert np.array_equal(a[k], want[k]), (depth, k)
+            assert np.array_equal(b[k], want[2 - k]), (depth, k)
+        # two height images in flight: the overflowed batch is redone from the image it was submitted with
+        dem2 = np.ascontiguousarray(-dem)
+        sc.set_height_from_r32f(dem2)
+        sc.set_camera_look_at(*cams[0])
+        want2 = sc.render_rgba().copy()
+        assert not np.array_equal(want2, want[0])
+        sc3 = ext.Scene(W, H, grid=G, colormap="magma")
+        sc3.set_shading("northstar", depth=depth); sc3.set_height_range(-0.3, 0.4)
+        sc3.set_height_from_r32f(dem)                                   # sizes the images; nothing rendered yet
+        sc3.set_height_from_r32f_async(dem)
+        t1 = sc3.render_batch_rgba_async(cams[:1])
+        sc3.set_height_from_r32f_async(dem2)
+        t2 = sc3.render_batch_rgba_async(cams[:1])
+        sc3.set_shading("shipped", depth=not depth)                      # state changes after submission do not leak into a redo
+        assert np.array_equal(sc3.collect(t1)[0], want[0]), depth
+        assert np.array_equal(sc3.collect(t2)[0], want2), depth
+
+
 # ---- reference API behaviour (tests/test_t31_integration.py, test_t41_scene.py, test_camera.py) ----
 def test_uniform_lanes_and_camera_updates(ext, vf):
     spike = ext.TerrainSpike(256, 192, grid=64, colormap="viridis")

@@ -176,7 +176,76 @@ def fuzz_dem(budget, seed):
     return bad
 
 
+def fuzz_api(budget, seed):
+    """Python API: grid_generate and the triangle against the oracle; pipelined batches (async upload +
+    async batch + collect, close-up cameras that overflow the primitive / pair buffers and make them
+    grow) against the synchronous single-frame path of a second Scene."""
+    ext = vf._vulkan_forge
+    rng = np.random.default_rng(seed)
+    t0 = time.time(); n = 0; bad = 0
+    while time.time() - t0 < budget:
+        what = int(rng.integers(0, 4))
+        if what == 0:
+            nx, nz = int(rng.integers(2, 400)), int(rng.integers(2, 400))
+            sp = (float(rng.choice([1.0, 0.5, 2.0, 0.1, 3.7])), float(rng.choice([1.0, 0.25, 2.0, 1.3])))
+            got = vf.grid_generate(nx, nz, spacing=sp)
+            ref = o.make_grid(nx, nz, sp[0], sp[1])
+            ok = all(np.array_equal(a, b) for a, b in zip(got, ref))
+            desc = dict(what="grid", nx=nx, nz=nz, sp=sp)
+        elif what == 1:
+            w, h = int(rng.integers(1, 900)), int(rng.integers(1, 700))
+            ok = np.array_equal(vf.render_triangle_rgba(w, h), o.render_triangle(w, h))
+            desc = dict(what="triangle", w=w, h=h)
+        else:
+            W, H = int(rng.integers(8, 500)), int(rng.integers(8, 400))
+            G = int(rng.choice([rng.integers(16, 300), rng.integers(300, 1600)]))
+            depth = bool(rng.integers(0, 2)); mode = str(rng.choice(["northstar", "shipped"]))
+            dems = [synthetic_dem(int(rng.integers(0, 7)), G) * np.float32(rng.choice([1.0, 3.0])) for _ in range(2)]
+            cams = []
+            for _ in range(int(rng.integers(1, 5))):
+                if rng.random() < 0.6:      # close-up: most triangles are big -> queues and pair buffers grow
+                    e = (float(rng.uniform(-0.3, 0.3)), float(rng.uniform(0.05, 0.6)), float(rng.uniform(-0.3, 0.3)))
+                    t = (e[0] + float(rng.uniform(-1, 1)), float(rng.uniform(-0.3, 0.1)), e[2] + float(rng.uniform(-1, 1)))
+                else:
+                    a = float(rng.uniform(0, 6.28)); e = (4 * math.cos(a), float(rng.uniform(0.5, 3)), 4 * math.sin(a)); t = (0.0, 0.0, 0.0)
+                cams.append((e, t, (0.0, 1.0, 0.0), float(rng.choice([45.0, 90.0])), float(rng.choice([0.01, 0.1])), 100.0))
+            desc = dict(what="pipeline", W=W, H=H, G=G, depth=depth, mode=mode, cams=cams)
+            def scene():
+                sc = ext.Scene(W, H, grid=G, colormap="viridis")
+                sc.set_shading(mode, depth=depth); sc.set_height_range(-0.4, 0.5)
+                return sc
+            ref_sc, sc = scene(), scene()
+            want = []
+            for d in dems:
+                ref_sc.set_height_from_r32f(d)
+                fr = []
+                for c in cams:
+                    ref_sc.set_camera_look_at(*c)
+                    fr.append(ref_sc.render_rgba().copy())
+                want.append(np.stack(fr))
+            ok = True
+            pending = []
+            for k in range(4):
+                sc.set_height_from_r32f_async(dems[k & 1])
+                pending.append((k & 1, sc.render_batch_rgba_async(cams)))
+                if len(pending) == 3:
+                    which, tk = pending.pop(0)
+                    ok = ok and np.array_equal(sc.collect(tk), want[which])
+            for which, tk in pending:
+                ok = ok and np.array_equal(sc.collect(tk), want[which])
+            ok = ok and np.array_equal(sc.render_batch_rgba(cams), want[1])
+            del sc, ref_sc
+        n += 1
+        if not ok:
+            bad += 1
+            print("API MISMATCH", json.dumps(desc), flush=True)
+    print(f"fuzz api: {n} cases in {time.time() - t0:.0f} s, {bad} mismatches, seed {seed}")
+    return bad
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "api":
+        sys.exit(1 if fuzz_api(float(sys.argv[2]) if len(sys.argv) > 2 else 30.0, int(sys.argv[3]) if len(sys.argv) > 3 else 1) else 0)
     if len(sys.argv) > 1 and sys.argv[1] == "dem":
         sys.exit(1 if fuzz_dem(float(sys.argv[2]) if len(sys.argv) > 2 else 30.0, int(sys.argv[3]) if len(sys.argv) > 3 else 1) else 0)
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60.0

@@ -62,7 +62,14 @@ struct vf_scene {
     cudaEvent_t ev_uploaded = nullptr, ev_front_released = nullptr;
     // batches in flight (vf_scene_render_batch_async): completion event on the copy stream, the
     // high-water marks of the batch in a pinned slot, and what is needed to redo it after growing a buffer
-    struct Ticket { cudaEvent_t done = nullptr; bool busy = false; std::vector<float> u; int n = 0; uint8_t* out = nullptr; };
+    struct Ticket {
+        cudaEvent_t done = nullptr; bool busy = false; std::vector<float> u; int n = 0; uint8_t* out = nullptr;
+        // state of the scene when the batch was submitted: an overflow is judged against THESE capacities
+        // (a later batch may have grown the buffers since) and the batch is redone from THIS height image
+        uint32_t cap_pairs = 0, cap_big = 0; const float* dem = nullptr;
+        int mode = 0, depth = 0; float h_min = 0.0f, h_max = 0.0f;
+        bool resolved = false; int rc = 0;
+    };
     Ticket tickets[4];
     bool slot_used[2] = {false, false};
     uint32_t* d_flag = nullptr;
@@ -167,9 +174,12 @@ static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pit
     return ok;
 }
 
+static void scene_resolve_readers(vf_scene* s, const float* image);
+
 static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "height image cannot be empty");
     const uint32_t pitch = (w + 3u) & ~3u;            // rows start 16-byte aligned (TMA-ready)
+    scene_resolve_readers(s, nullptr);                // batches in flight read the images replaced below
     if (s->upload_stream) VF_CUDA(cudaStreamSynchronize(s->upload_stream));
     s->back_pending = false;
     if (pitch != s->pitch || h != s->Hd || !s->d_dem) {
@@ -246,10 +256,12 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     build_lut(pal, lut_unorm, lut);
     cudaError_t e = cudaMemcpy(s->d_lut, lut, sizeof lut, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) { scene_free(s); return vf_set_error(VF_E_CUDA, "LUT upload: %s", cudaGetErrorString(e)); }
-    const uint64_t cap = std::max<uint64_t>(1u << 20, 4ull * (uint64_t)w * (uint64_t)h);
+    // VF_TEST_SMALL_BUFFERS: tests start with tiny queues so that every close-up takes the grow-and-retry path
+    const bool tiny = getenv("VF_TEST_SMALL_BUFFERS") != nullptr;
+    const uint64_t cap = tiny ? 256 : std::max<uint64_t>(1u << 20, 4ull * (uint64_t)w * (uint64_t)h);
     rc = scene_alloc_pairs(s, (uint32_t)std::min<uint64_t>(cap, 1u << 30));
     if (rc) { scene_free(s); return rc; }
-    rc = scene_alloc_big(s, 1u << 20);
+    rc = scene_alloc_big(s, tiny ? 4u : 1u << 20);
     if (rc) { scene_free(s); return rc; }
     if (cudaMalloc(&s->d_visbuf, (size_t)w * h * 8) != cudaSuccess) {
         scene_free(s);
@@ -515,8 +527,9 @@ static int scene_apply_pending_dem(vf_scene* s) {
 // Enqueues n frames (+ their D2H copies when out_host is given) and the read-back of the batch's
 // counters into pinned slot `hslot`.  Frame k is rendered into slot k%2 while the copy stream
 // drains the other slot to the host.  Does not wait.
-static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, int hslot) {
-    int rc = scene_apply_pending_dem(s);
+static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, int hslot,
+                        bool apply_pending = true) {
+    int rc = apply_pending ? scene_apply_pending_dem(s) : VF_OK;
     if (rc) return rc;
     const size_t fbytes = (size_t)s->W * s->H * 4;
     VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
@@ -563,12 +576,12 @@ static int scene_check_overflow(vf_scene* s, int hslot) {
 // Renders n frames and waits; out_host may be null (frames stay on the device).  If a kernel asked
 // for more queue / pair space than its buffer holds, the buffer is grown and the call is repeated
 // (an overflowed frame leaves a clean visibility buffer: k_raster always runs to completion).
-static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis) {
+static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, bool apply_pending = true) {
     if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
     int rc = vf_require_device();
     if (rc) return rc;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0);
+        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending);
         if (rc) return rc;
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
@@ -581,6 +594,44 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 }
 
 // ---- pipelined interface: uploads and batches overlap across calls -------------------------------
+static void scene_swap_images(vf_scene* s) {
+    std::swap(s->d_dem, s->d_dem_back);
+    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b);
+}
+
+// Waits for batch `id`.  If one of its kernels ran out of queue / pair space (judged against the
+// buffers the batch was submitted with), the buffers are grown and the batch is rendered again,
+// synchronously, with the mode and from the height image it was submitted with.  That image is
+// still intact: whatever would overwrite it resolves the batches that read it first.
+static int ticket_resolve(vf_scene* s, int id) {
+    vf_scene::Ticket& t = s->tickets[id];
+    if (t.resolved) return t.rc;
+    t.resolved = true;
+    t.rc = VF_OK;
+    if (cudaEventSynchronize(t.done) != cudaSuccess) return t.rc = vf_set_error(VF_E_CUDA, "batch %d: %s", id, cudaGetErrorString(cudaGetLastError()));
+    const uint32_t* h = s->h_counters + (size_t)(1 + id) * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
+    if (h[0] <= t.cap_pairs && h[1] <= t.cap_big) return VF_OK;
+    const int ov = scene_check_overflow(s, 1 + id);       // grows what is still too small (a later batch may have done it already)
+    if (ov < 0) return t.rc = -ov;
+    const bool other = t.dem != s->d_dem;
+    if (other && (t.dem != s->d_dem_back || s->back_pending))
+        return t.rc = vf_set_error(VF_E_INVALID, "batch %d overflowed and its height image is gone", id);
+    const int mode = s->mode, depth = s->depth;
+    const float h_min = s->h_min, h_max = s->h_max;
+    s->mode = t.mode; s->depth = t.depth; s->h_min = t.h_min; s->h_max = t.h_max;
+    if (other) scene_swap_images(s);
+    t.rc = scene_render(s, t.u.data(), t.n, t.out, nullptr, false);
+    if (other) scene_swap_images(s);
+    s->mode = mode; s->depth = depth; s->h_min = h_min; s->h_max = h_max;
+    return t.rc;
+}
+
+// before `image` is overwritten: finish (and if need be redo) the batches that read it
+static void scene_resolve_readers(vf_scene* s, const float* image) {
+    for (int k = 0; k < 4; ++k)
+        if (s->tickets[k].busy && (!image || s->tickets[k].dem == image)) ticket_resolve(s, k);
+}
+
 extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (!s || !host) return vf_set_error(VF_E_INVALID, "null argument");
     const uint32_t pitch = (w + 3u) & ~3u;
@@ -599,6 +650,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
             return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
         s->back_valid = true;
     }
+    scene_resolve_readers(s, s->d_dem_back);      // normally none: those batches were collected long ago
     // the back image was the front image of frames submitted before the last swap
     if (s->front_released_once) VF_CUDA(cudaStreamWaitEvent(s->upload_stream, s->ev_front_released, 0));
     VF_CUDA(cudaMemcpy2DAsync(s->d_dem_back, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
@@ -620,6 +672,9 @@ extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int 
     t.u.assign(u44xn, u44xn + (size_t)n * 44); t.n = n; t.out = out_rgba_host;
     rc = scene_submit(s, u44xn, n, out_rgba_host, nullptr, 1 + id);
     if (rc) return rc;
+    t.cap_pairs = s->capacity; t.cap_big = s->big_capacity; t.dem = s->d_dem;       // after the swap inside scene_submit
+    t.mode = s->mode; t.depth = s->depth; t.h_min = s->h_min; t.h_max = s->h_max;
+    t.resolved = false; t.rc = VF_OK;
     // done = counters read back on the render stream and every frame copied on the copy stream
     VF_CUDA(cudaEventRecord(s->ev_done[0], s->stream));           // reuse as a plain marker: ordered after the read-back
     VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[0], 0));
@@ -631,13 +686,9 @@ extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int 
 
 extern "C" int vf_scene_wait(vf_scene* s, int ticket) {
     if (!s || ticket < 0 || ticket >= 4 || !s->tickets[ticket].busy) return vf_set_error(VF_E_INVALID, "invalid ticket");
-    vf_scene::Ticket& t = s->tickets[ticket];
-    VF_CUDA(cudaEventSynchronize(t.done));
-    t.busy = false;
-    const int ov = scene_check_overflow(s, 1 + ticket);
-    if (ov < 0) return -ov;
-    if (ov == 1) return scene_render(s, t.u.data(), t.n, t.out, nullptr);   // rare: redo synchronously with the grown buffers
-    return VF_OK;
+    const int rc = ticket_resolve(s, ticket);
+    s->tickets[ticket].busy = false;
+    return rc;
 }
 
 extern "C" int vf_scene_render_rgba(vf_scene* s, uint8_t* out_rgba_host) {

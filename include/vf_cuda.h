@@ -128,7 +128,10 @@ int vf_scene_render_batch(vf_scene *s, const float *u44xn, int n, uint8_t *out_r
 /* Pipelined variants (batches of independent frames): the upload goes to a second
  * device image on its own stream while frames of the current image render; the batch call returns
  * once everything is enqueued.  Host buffers must be pinned and stay untouched until vf_scene_wait
- * (output) / the next vf_scene_wait after the batch that uses them (height).  At most 4 batches in flight. */
+ * (output) / the next vf_scene_wait after the batch that uses them (height).  At most 4 batches in flight.
+ * A batch renders with the mode, height range and height image current when it was submitted; if one
+ * of its frames needed more queue / pair space than the scene had at that moment, vf_scene_wait grows
+ * the buffers and renders the batch again (synchronously, from that same image) before it returns. */
 int vf_scene_set_height_f32_async(vf_scene *s, const float *host_pinned, uint32_t w, uint32_t h);
 int vf_scene_render_batch_async(vf_scene *s, const float *u44xn, int n, uint8_t *out_rgba_host_pinned, int *ticket);
 int vf_scene_wait(vf_scene *s, int ticket);

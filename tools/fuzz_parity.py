@@ -243,7 +243,61 @@ def fuzz_api(budget, seed):
     return bad
 
 
+def fuzz_renderer(budget, seed):
+    """Renderer height path: add_terrain (f32 / f64, exaggeration) -> terrain_stats / height_range ->
+    normalize_terrain(minmax) -> upload_height_r32f -> read back, against the oracle (min, max, range and
+    the min-max normalised image bit-for-bit; mean / std to the reference tests' 1e-3)."""
+    rng = np.random.default_rng(seed)
+    t0 = time.time(); n = 0; bad = 0
+    r = vf.Renderer(8, 8)
+    while time.time() - t0 < budget:
+        hh, ww = int(rng.choice([rng.integers(1, 6), rng.integers(6, 400)])), int(rng.choice([rng.integers(1, 6), rng.integers(6, 400)]))
+        dt = np.float64 if rng.random() < 0.4 else np.float32
+        kind = int(rng.integers(0, 4))
+        if kind == 0:
+            z = rng.normal(rng.normal(0, 5), 10.0 ** rng.uniform(-3, 3), (hh, ww))
+        elif kind == 1:
+            z = np.round(rng.normal(0, 2, (hh, ww)))
+        elif kind == 2:
+            z = np.full((hh, ww), rng.normal())
+        else:
+            z = rng.normal(0, 1, (hh, ww)); z.flat[rng.integers(0, z.size)] = 1e4
+        z = np.ascontiguousarray(z, dt)
+        ex = float(rng.choice([1.0, 2.0, 0.5, 3.3]))
+        r.add_terrain(z, (1.0, 1.0), ex, "viridis")
+        h32 = (z.astype(np.float32) * np.float32(ex)).astype(np.float32)      # src/lib.rs:362,384
+        got = r.terrain_stats(); ref = o.dem_stats(h32)
+        scale = max(1e-30, float(np.abs(h32).max()))
+        ok = np.float32(got[0]).tobytes() == ref[0].tobytes() and np.float32(got[1]).tobytes() == ref[1].tobytes()
+        # the reference (and the oracle) accumulate sequentially in f32: their own error grows with n
+        tol = (1e-3 + 6e-8 * h32.size) * scale
+        ok = ok and abs(got[2] - float(ref[2])) <= tol and abs(got[3] - float(ref[3])) <= tol + 1e-3 * float(ref[3])
+        ok = ok and r.height_range() == tuple(float(x) for x in o.h_range(h32))
+        desc = dict(what="stats", shape=(hh, ww), dtype=str(np.dtype(dt)), kind=kind, ex=ex, got=[float(x) for x in got], ref=[float(x) for x in ref])
+        if ok:
+            lo = float(rng.choice([0.0, -1.0, 10.0])); hi = lo + float(rng.choice([1.0, 10.0, 0.001]))
+            r.normalize_terrain("minmax", range=(lo, hi))
+            r.upload_height_r32f()
+            full = r.read_full_height_texture()
+            want = o.normalize(h32, "minmax", rng=(lo, hi))
+            ok = np.array_equal(full, want)
+            desc = dict(what="normalize", shape=(hh, ww), dtype=str(np.dtype(dt)), kind=kind, ex=ex, range=(lo, hi), diff=int((full != want).sum()))
+            if ok and hh > 1 and ww > 1:
+                x0, y0 = int(rng.integers(0, ww - 1)), int(rng.integers(0, hh - 1))
+                pw, ph = int(rng.integers(1, ww - x0 + 1)), int(rng.integers(1, hh - y0 + 1))
+                ok = np.array_equal(r.debug_read_height_patch(x0, y0, pw, ph), want[y0:y0 + ph, x0:x0 + pw])
+                desc["what"] = "patch"
+        n += 1
+        if not ok:
+            bad += 1
+            print("RENDERER MISMATCH", json.dumps(desc), flush=True)
+    print(f"fuzz renderer: {n} cases in {time.time() - t0:.0f} s, {bad} mismatches, seed {seed}")
+    return bad
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "renderer":
+        sys.exit(1 if fuzz_renderer(float(sys.argv[2]) if len(sys.argv) > 2 else 30.0, int(sys.argv[3]) if len(sys.argv) > 3 else 1) else 0)
     if len(sys.argv) > 1 and sys.argv[1] == "api":
         sys.exit(1 if fuzz_api(float(sys.argv[2]) if len(sys.argv) > 2 else 30.0, int(sys.argv[3]) if len(sys.argv) > 3 else 1) else 0)
     if len(sys.argv) > 1 and sys.argv[1] == "dem":

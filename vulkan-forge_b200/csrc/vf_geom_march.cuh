@@ -107,9 +107,17 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
             vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
             VfEdges es;
             vf_edges_setup(t, x0, y0, es);
+#ifdef VF_GM_THIN64                                          // A/B: the 64-bit walk of the tiled k_geom
             vf_thin_raster(es, x0, x1, y0, y1, [&](int px, int py, int64_t ed[3]) {
                 vf_gm_emit<DEPTH>(f, vis, t, es, prim, px, py, ed);
             });
+#else
+            vf_thin_raster32(es, x0, x1, y0, y1, [&](int px, int py) {
+                int64_t ed[3];
+                if (DEPTH) vf_edges_at(es, px - x0, py - y0, ed);
+                vf_gm_emit<DEPTH>(f, vis, t, es, prim, px, py, ed);
+            });
+#endif
         }
         q.nhead = (q.nhead + take) & (VF_GM_NCAP - 1u);
         q.nn -= take;
@@ -239,8 +247,16 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     const uint32_t below = (1u << lane) - 1u;
 
     // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
-    auto ask_task = [&]() -> uint32_t { return lane == 0 ? atomicAdd(&counters[VF_CNT_TASK], 1u) : 0u; };
-    auto got_task = [&](uint32_t t) -> uint32_t { return __shfl_sync(0xffffffffu, t, 0); };
+    // The counter is kept as a FLOAT (exact below 2^24 tasks; the host falls back to more rows per task
+    // above that): ptxas turns every integer atomic add, from atomicAdd() or from asm, into a
+    // warp-aggregated atomic whose closing shuffle waits for the answer at once, which would put
+    // the round trip back on the critical path.
+    auto ask_task = [&]() -> uint32_t {
+        float t = 0.0f;
+        if (lane == 0) asm volatile("atom.global.add.f32 %0, [%1], 0f3F800000;" : "=f"(t) : "l"(counters + VF_CNT_TASK));
+        return __float_as_uint(t);
+    };
+    auto got_task = [&](uint32_t t) -> uint32_t { return (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
     auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
         if (TMA && lane == 0 && task < ntasks) {
             uint32_t strip, j0, nr;

@@ -412,6 +412,9 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         s->segtab_n = (uint32_t)tab.size(); s->segtab_G = s->G; s->segtab_workers = workers;
     }
     const uint32_t nsegs = s->segtab_n, ntasks = nstrips * nsegs;
+    // the task dispenser counts in float (vf_geom_march.cuh): exact while every request stays below 2^24
+    // (grid <= 32768: at most 1058 strips x 8192 segments)
+    if ((uint64_t)ntasks + 2ull * workers + 2ull >= (1ull << 24)) return vf_set_error(VF_E_INVALID, "grid too fine for the task dispenser");
     const uint32_t ctas = std::min<uint32_t>((uint32_t)sm_count * per_sm, (ntasks + VF_GM_WARPS - 1) / VF_GM_WARPS);
     // profiling aid (builds with VF_NVCC_EXTRA=-DVF_GM_PROFILE only): VF_GM_DBG=<file> dumps [ctas*8][start,end] ns + per-task ns of the last launch
 #ifdef VF_GM_PROFILE

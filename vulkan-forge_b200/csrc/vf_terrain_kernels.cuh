@@ -149,6 +149,69 @@ __device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1,
 }
 
 // ---------------------------------------------------------------------------------------
+// The same walk with a 32-bit inner loop (k_geom_march).  Requires vf_serial_ok (|area2| < 2^29).
+//   run bounds : crossing of edge i with line m in float, tc_i(m) = fma(m, slope_i, tc0_i); its error
+//                stays below (|tc0_i| + nmin |slope_i|) 2^-20 px, which is added to the 1/64 px margin
+//                of that edge, so the run [c0, c1] never loses a covered sample;
+//   samples    : a sample of the run is within margin_i px (along the run) of satisfying every
+//                non-flat edge, so E_i >= -margin_i 256 |amaj_i| > -2^27, and E_i = |area2| - E_j - E_k
+//                < 2^31: the low 32 bits of the biased edge values carry their signs, and the test
+//                runs on wrapped 32-bit sums (one IADD per edge and step);
+//   flat edges : an edge parallel to the run (amaj == 0) is constant on a line; its exact 64-bit
+//                sign is taken once per line and it is left out of the 32-bit test.
+// emit(px, py) gets no edge values (depth: vf_edges_at on the covered sample restores them).
+template <typename Emit>
+__device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x1, int y0, int y1, Emit&& emit) {
+    const bool cols = (x1 - x0) <= (y1 - y0);        // minor axis = x: walk columns, runs along y
+    const int nmin = cols ? x1 - x0 + 1 : y1 - y0 + 1;
+    const int nmaj = cols ? y1 - y0 + 1 : x1 - x0 + 1;
+    uint32_t e32[3], smin[3], smaj[3];                // low words: value at (line 0, sample 0), step per line / per sample
+    float tc0[3], slope[3];
+    bool lower[3], upper[3], flat = false;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int32_t amaj = cols ? s.B[i] : s.A[i], amin = cols ? s.A[i] : s.B[i];
+        lower[i] = amaj > 0; upper[i] = amaj < 0;
+        flat = flat || amaj == 0;
+        const float r = amaj != 0 ? __fdividef(-1.0f, __fmul_rn((float)amaj, (float)VF_SUBPIX)) : 0.0f;
+        const float t0 = __fmul_rn((float)s.E[i], r), sl = __fmul_rn(__fmul_rn((float)amin, (float)VF_SUBPIX), r);
+        const float mg = fmaf(fmaf((float)nmin, fabsf(sl), fabsf(t0)), 0x1p-20f, 0.015625f);
+        tc0[i] = lower[i] ? __fsub_rn(t0, mg) : __fadd_rn(t0, mg);
+        slope[i] = sl;
+        e32[i] = amaj != 0 ? (uint32_t)s.E[i] : 0u;
+        smin[i] = amaj != 0 ? (uint32_t)amin * (uint32_t)VF_SUBPIX : 0u;
+        smaj[i] = (uint32_t)amaj * (uint32_t)VF_SUBPIX;
+    }
+    for (int m = 0; m < nmin; ++m) {
+        const float fm = (float)m;
+        float lo = 0.0f, hi = (float)(nmaj - 1);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const float tc = fmaf(fm, slope[i], tc0[i]);
+            if (lower[i]) lo = fmaxf(lo, tc);
+            if (upper[i]) hi = fminf(hi, tc);
+        }
+        if (flat) {
+            bool dead = false;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                if (!lower[i] && !upper[i])
+                    dead = dead || s.E[i] + (int64_t)(cols ? s.A[i] : s.B[i]) * (int64_t)(m * VF_SUBPIX) < 0;
+            if (dead) continue;
+        }
+        if (!(lo <= hi)) continue;
+        const int c0 = __float2int_ru(lo), c1 = __float2int_rd(hi);      // 0 <= lo, hi <= nmaj - 1
+        uint32_t ed0 = e32[0] + smin[0] * (uint32_t)m + smaj[0] * (uint32_t)c0;
+        uint32_t ed1 = e32[1] + smin[1] * (uint32_t)m + smaj[1] * (uint32_t)c0;
+        uint32_t ed2 = e32[2] + smin[2] * (uint32_t)m + smaj[2] * (uint32_t)c0;
+        for (int c = c0; c <= c1; ++c) {
+            if ((int32_t)(ed0 | ed1 | ed2) >= 0) emit(cols ? x0 + m : x0 + c, cols ? y0 + c : y0 + m);
+            ed0 += smaj[0]; ed1 += smaj[1]; ed2 += smaj[2];
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 struct VfGeomSmem {
     alignas(128) float dem[VF_TMA_BOX_Y][VF_TMA_BOX_X];   // TMA destination (DEM tile of this CTA)
     VfAxis ax[VF_GEOM_VX], az[VF_GEOM_VY];    // axis entries of the tile's columns / rows

@@ -256,7 +256,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         if (lane == 0) asm volatile("atom.global.add.f32 %0, [%1], 0f3F800000;" : "=f"(t) : "l"(counters + VF_CNT_TASK));
         return __float_as_uint(t);
     };
-    auto got_task = [&](uint32_t t) -> uint32_t { return (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
+    // Worker k starts with tasks k and k + workers (no round trip, no burst of requests at the start of the
+    // launch); the counter hands out the rest.
+    const uint32_t nworkers = gridDim.x * VF_GM_WARPS, wid = blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5);
+    auto got_task = [&](uint32_t t) -> uint32_t { return 2u * nworkers + (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
     auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
         if (TMA && lane == 0 && task < ntasks) {
             uint32_t strip, j0, nr;
@@ -275,13 +278,23 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     }
     VfGmQueues q = {0u, 0u, 0u, 0u};
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
-    uint32_t cur = got_task(ask_task());
+    uint32_t cur = wid, nxt = nworkers + wid;
     issue(cur, 0u);
-    uint32_t nxt = got_task(ask_task());
+    // axis entries of the columns / rows of a task are fetched one task ahead as well
+    auto fetch_axes = [&](uint32_t task, VfAxis& ax, VfAxis& az) {
+        if (task < ntasks) {
+            uint32_t strip, j0, nr;
+            decode(task, strip, j0, nr);
+            ax = axis[min(strip * VF_GM_QCOLS + lane, gm)];
+            az = axis[min(j0 + min(lane, (uint32_t)VF_GM_VROWS - 1u), gm)];
+        }
+    };
+    VfAxis ax = {0.0f, 0.0f, 0, 0}, az = ax;
+    fetch_axes(cur, ax, az);
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
     float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
-    float exag = f.exag, hw = f.hw, hh = f.hh;
+    float exag = f.exag, hw = __fmul_rn(f.hw, (float)VF_SUBPIX), hh = __fmul_rn(f.hh, (float)VF_SUBPIX);   // in sub-pixels
 #define VF_PIN(x) asm volatile("" : "+f"(x))
     VF_PIN(V4); VF_PIN(V5); VF_PIN(V6); VF_PIN(V8); VF_PIN(V9); VF_PIN(V10);
     VF_PIN(P0); VF_PIN(P5); VF_PIN(P10); VF_PIN(P11); VF_PIN(P14); VF_PIN(P15);
@@ -300,12 +313,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         const bool colv = i < f.G;
         const bool cellv = lane < VF_GM_QCOLS && i + 1u < f.G;
         // ---- per-column and per-row constants ----
-        const VfAxis ax = axis[min(i, gm)];
         const float wx = __fmul_rn(ax.coord, f.spacing);
         const float a0 = fmaf(f.V[0], wx, f.V[12]), a1 = fmaf(f.V[1], wx, f.V[13]), a2 = fmaf(f.V[2], wx, f.V[14]);
         const float sx25 = SHIPPED ? __fmul_rn(sinf(__fmul_rn(ax.coord, 1.3f)), 0.25f) : 0.0f;
         if (lane < VF_GM_VROWS) {
-            const VfAxis az = axis[min(j0 + lane, gm)];
             w.wz[lane] = __fmul_rn(az.coord, f.spacing);
             w.ty[lane] = az.ty;
             if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az.coord, 1.1f)), 0.25f);
@@ -321,6 +332,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the guard band)
         const float* texel = &w.dem[stage][((strip * VF_GM_QCOLS) & 3u) + lane];
         const float* gtexel = dem + ax.tx;
+        fetch_axes(nxt, ax, az);                            // used at the start of the next task
         const uint32_t cell0 = (j0 - 1u) * gm + i;          // cell index of (row r-1, column i) is cell0 + r*gm
         uint32_t r = 0u;
         auto load_h = [&](uint32_t rr) -> float {
@@ -339,8 +351,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         // viewport + snap (vf_to_screen) given 1/w
         auto snap = [&](const float c[4], float invw, int32_t& X, int32_t& Y, float& Z) {
             const float xn = __fmul_rn(c[0], invw), yn = __fmul_rn(c[1], invw);
-            X = __float2int_rn(__fmul_rn(fmaf(xn, hw, hw), (float)VF_SUBPIX));
-            Y = __float2int_rn(__fmul_rn(fmaf(-yn, hh, hh), (float)VF_SUBPIX));
+            // fma(xn, hw, hw) * 256 == fma(xn, 256 hw, 256 hw): scaling by a power of two commutes with the
+            // rounding (256 hw is exact, the sum is never subnormal: it is 0 or at least hw 2^-24)
+            X = __float2int_rn(fmaf(xn, hw, hw));
+            Y = __float2int_rn(fmaf(-yn, hh, hh));
             Z = DEPTH ? __fmul_rn(c[2], invw) : 0.0f;
         };
         auto append = [&](uint32_t m, bool keep, uint32_t cell, int32_t aX, int32_t aY, float aZ, int32_t bX, int32_t bY, float bZ,

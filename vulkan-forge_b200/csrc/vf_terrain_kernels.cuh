@@ -570,7 +570,7 @@ k_binsort(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, co
 //             atomicMin((depth<<32)|prim) (depth Less);
 //   shading : thread = pixel; rebuilds the winning primitive, perspective-correct varyings,
 //             fragment stage, exact sRGB8; 4 pixels are packed per 16-byte store.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 5)
 k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
          const float* __restrict__ dem, const float4* __restrict__ lut,
          const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,

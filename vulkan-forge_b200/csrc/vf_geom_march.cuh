@@ -45,10 +45,10 @@ struct VfGmWarpT {
     alignas(8) uint64_t mbar[2];
     float wz[VF_GM_VROWS], kz[VF_GM_VROWS];              // per row: z*spacing, 0.25*cos(1.1 z)
     int ty[VF_GM_VROWS];                                 // per row: texel row
-    int32_t qx[4][VF_GM_QCAP], qy[4][VF_GM_QCAP];        // queued cells: snapped a, b, c, d
+    alignas(8) int2 qv[4][VF_GM_QCAP];                   // queued cells: snapped (X, Y) of a, b, c, d
     float qz[DEPTH ? 4 : 1][DEPTH ? VF_GM_QCAP : 1];     // depth only
     uint32_t qcell[VF_GM_QCAP];                          // cell index | bit 31: rebuild from scratch (clip flags mixed)
-    int32_t nx[3][VF_GM_NCAP], ny[3][VF_GM_NCAP];        // queued long triangles
+    alignas(8) int2 nv[3][VF_GM_NCAP];                   // queued long triangles: snapped (X, Y) of the vertices
     float nz[DEPTH ? 3 : 1][DEPTH ? VF_GM_NCAP : 1];     // depth only
     uint32_t nprim[VF_GM_NCAP];
 };
@@ -79,11 +79,12 @@ static __device__ __noinline__ int vf_gm_rebuild(const VfFrame& f, const VfAxis*
 // one covered sample -> visibility buffer
 template <bool DEPTH>
 __device__ __forceinline__ void vf_gm_emit(const VfFrame& f, unsigned long long* __restrict__ vis, const VfSubTri& t,
-                                           const VfEdges& es, uint32_t prim, int px, int py, int64_t ed[3]) {
+                                           uint32_t nbias, uint32_t prim, int px, int py, int64_t ed[3]) {
     float zf = 0.0f;
     if (DEPTH) {
         float b[3];
-        vf_edges_unbias(es, ed);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) ed[i] += (int64_t)((nbias >> i) & 1u);     // vf_edges_unbias
         vf_barycentric(ed, b);
         zf = vf_depth_at(t, b);
         if (!(zf < 1.0f)) return;
@@ -101,7 +102,7 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
             const uint32_t s = (q.nhead + lane) & (VF_GM_NCAP - 1u);
             VfSubTri t;
 #pragma unroll
-            for (int k = 0; k < 3; ++k) { t.v[k].X = w.nx[k][s]; t.v[k].Y = w.ny[k][s]; t.v[k].zn = DEPTH ? w.nz[k][s] : 0.0f; }
+            for (int k = 0; k < 3; ++k) { const int2 v = w.nv[k][s]; t.v[k].X = v.x; t.v[k].Y = v.y; t.v[k].zn = DEPTH ? w.nz[k][s] : 0.0f; }
             const uint32_t prim = w.nprim[s];
             int x0, x1, y0, y1;
             vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
@@ -109,13 +110,13 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
             vf_edges_setup(t, x0, y0, es);
 #ifdef VF_GM_THIN64                                          // A/B: the 64-bit walk of the tiled k_geom
             vf_thin_raster(es, x0, x1, y0, y1, [&](int px, int py, int64_t ed[3]) {
-                vf_gm_emit<DEPTH>(f, vis, t, es, prim, px, py, ed);
+                vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
             });
 #else
             vf_thin_raster32(es, x0, x1, y0, y1, [&](int px, int py) {
                 int64_t ed[3];
                 if (DEPTH) vf_edges_at(es, px - x0, py - y0, ed);
-                vf_gm_emit<DEPTH>(f, vis, t, es, prim, px, py, ed);
+                vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
             });
 #endif
         }
@@ -152,24 +153,45 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                 for (int v = 0; v < 3; ++v) { t.v[v].X = tr.v[v].X; t.v[v].Y = tr.v[v].Y; t.v[v].zn = tr.v[v].zn; }
             } else {                                     // T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
                 const uint32_t i0 = k, i2 = 1u + 2u * k;
-                t.v[0].X = w.qx[i0][slot]; t.v[0].Y = w.qy[i0][slot];
-                t.v[1].X = w.qx[2][slot];  t.v[1].Y = w.qy[2][slot];
-                t.v[2].X = w.qx[i2][slot]; t.v[2].Y = w.qy[i2][slot];
+                const int2 v0 = w.qv[i0][slot], v1 = w.qv[2][slot], v2 = w.qv[i2][slot];
+                t.v[0].X = v0.x; t.v[0].Y = v0.y;
+                t.v[1].X = v1.x; t.v[1].Y = v1.y;
+                t.v[2].X = v2.x; t.v[2].Y = v2.y;
                 if (DEPTH) { t.v[0].zn = w.qz[i0][slot]; t.v[1].zn = w.qz[2][slot]; t.v[2].zn = w.qz[i2][slot]; }
             }
             if (st == 2) {
                 to_big = true;                           // needs clipping
             } else if (st == 1) {
                 int x0, x1, y0, y1;
-                if (vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1) && vf_area2(t) < 0) {
+                const int32_t mnx = min(t.v[0].X, min(t.v[1].X, t.v[2].X)), mxx = max(t.v[0].X, max(t.v[1].X, t.v[2].X));
+                const int32_t mny = min(t.v[0].Y, min(t.v[1].Y, t.v[2].Y)), mxy = max(t.v[0].Y, max(t.v[1].Y, t.v[2].Y));
+                if (vf_bbox_pixels(mnx, mxx, mny, mxy, f.W, f.H, x0, x1, y0, y1) && vf_area2(t) < 0) {
                     const int bw = x1 - x0 + 1, bh = y1 - y0 + 1, npx = bw * bh;
-                    if (npx <= VF_MICRO_MAX) {
-                        VfEdges es;
-                        vf_edges_setup(t, x0, y0, es);
+                    // Micro triangle that is small itself (not a large one with a few on-screen samples): its
+                    // extent is below 2^12 sub-pixels, the reference centre lies inside its bbox, so every
+                    // edge value stays below 2^26 and the coverage test runs in 32 bits.
+                    if (npx <= VF_MICRO_MAX && (uint32_t)((mxx - mnx) | (mxy - mny)) < 4096u) {
+                        const int32_t sx = x0 * VF_SUBPIX + VF_HALFPIX, sy = y0 * VF_SUBPIX + VF_HALFPIX;
+                        int32_t A[3], B[3], E[3];
+                        uint32_t nbias = 0u;
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) {           // vf_edges_setup in 32 bits
+                            const VfSVtx& a = t.v[(i + 1) % 3];
+                            const VfSVtx& b = t.v[(i + 2) % 3];
+                            A[i] = b.Y - a.Y; B[i] = a.X - b.X;
+                            const bool tl = vf_top_left(a, b);
+                            nbias |= tl ? 0u : (1u << i);
+                            E[i] = A[i] * (sx - a.X) + B[i] * (sy - a.Y) - (tl ? 0 : 1);
+                        }
                         for (int dy = 0; dy < bh; ++dy)
                             for (int dx = 0; dx < bw; ++dx) {
-                                int64_t ed[3];
-                                if (vf_edges_at(es, dx, dy, ed)) vf_gm_emit<DEPTH>(f, vis, t, es, prim, x0 + dx, y0 + dy, ed);
+                                const int32_t e0 = E[0] + A[0] * (dx * VF_SUBPIX) + B[0] * (dy * VF_SUBPIX);
+                                const int32_t e1 = E[1] + A[1] * (dx * VF_SUBPIX) + B[1] * (dy * VF_SUBPIX);
+                                const int32_t e2 = E[2] + A[2] * (dx * VF_SUBPIX) + B[2] * (dy * VF_SUBPIX);
+                                if ((e0 | e1 | e2) >= 0) {
+                                    int64_t ed[3] = {e0, e1, e2};
+                                    vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
+                                }
                             }
                     } else if (vf_serial_ok(t, bw, bh)) {
                         to_long = true;
@@ -187,7 +209,7 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                 const uint32_t s = (q.nhead + q.nn + __popc(nm & below)) & (VF_GM_NCAP - 1u);
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    w.nx[k][s] = t.v[k].X; w.ny[k][s] = t.v[k].Y;
+                    w.nv[k][s] = make_int2(t.v[k].X, t.v[k].Y);
                     if (DEPTH) w.nz[k][s] = t.v[k].zn;
                 }
                 w.nprim[s] = prim;
@@ -361,10 +383,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
                           int32_t cX, int32_t cY, float cZ, int32_t dX, int32_t dY, float dZ) {
             if (keep) {
                 const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
-                w.qx[0][s] = aX; w.qy[0][s] = aY;
-                w.qx[1][s] = bX; w.qy[1][s] = bY;
-                w.qx[2][s] = cX; w.qy[2][s] = cY;
-                w.qx[3][s] = dX; w.qy[3][s] = dY;
+                w.qv[0][s] = make_int2(aX, aY);
+                w.qv[1][s] = make_int2(bX, bY);
+                w.qv[2][s] = make_int2(cX, cY);
+                w.qv[3][s] = make_int2(dX, dY);
                 if (DEPTH) { w.qz[0][s] = aZ; w.qz[1][s] = bZ; w.qz[2][s] = cZ; w.qz[3][s] = dZ; }
                 w.qcell[s] = cell;
             }

@@ -282,10 +282,8 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     // launch); the counter hands out the rest.
     const uint32_t nworkers = gridDim.x * VF_GM_WARPS, wid = blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5);
     auto got_task = [&](uint32_t t) -> uint32_t { return 2u * nworkers + (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
-    auto issue = [&](uint32_t task, uint32_t stage) {       // lane 0: start the TMA of `task` into `stage`
-        if (TMA && lane == 0 && task < ntasks) {
-            uint32_t strip, j0, nr;
-            decode(task, strip, j0, nr);
+    auto issue = [&](bool valid, uint32_t strip, uint32_t j0, uint32_t stage) {   // lane 0: start the TMA of a task into `stage`
+        if (TMA && lane == 0 && valid) {
             vf_mbar_expect_tx(&w.mbar[stage], VF_GM_VROWS * VF_GM_BOX_X * 4u);
             vf_tma_load_2d(&w.dem[stage][0], &dem_map, (int)((strip * VF_GM_QCOLS) & ~3u), (int)j0, &w.mbar[stage]);
         }
@@ -300,19 +298,29 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     }
     VfGmQueues q = {0u, 0u, 0u, 0u};
     uint32_t stage = 0u, parity = 0u;                       // parity: bit s = phase of stage s
+    // Everything a task needs at its start is prepared one task ahead: its id (the dispenser's answer takes an
+    // L2 round trip), its place in the grid (a division and the segment table), its texels (TMA) and the axis
+    // entries of its columns / rows.  (asm volatile: a plain load is sunk by the compiler to its first use at
+    // the start of the next task, where its latency shows.)
     uint32_t cur = wid, nxt = nworkers + wid;
-    issue(cur, 0u);
-    // axis entries of the columns / rows of a task are fetched one task ahead as well
-    auto fetch_axes = [&](uint32_t task, VfAxis& ax, VfAxis& az) {
-        if (task < ntasks) {
-            uint32_t strip, j0, nr;
-            decode(task, strip, j0, nr);
-            ax = axis[min(strip * VF_GM_QCOLS + lane, gm)];
-            az = axis[min(j0 + min(lane, (uint32_t)VF_GM_VROWS - 1u), gm)];
+    uint32_t strip = 0u, j0 = 0u, nr = 0u;                  // place of `cur`
+    float ax_coord = 0.0f, az_coord = 0.0f;                 // axis entries of `cur`: column of this lane, row `lane`
+    int ax_tx = 0, az_ty = 0;
+    auto fetch_axes = [&](uint32_t s0, uint32_t r0) {
+        const VfAxis* pa = axis + min(s0 * VF_GM_QCOLS + lane, gm);
+        const VfAxis* pz = axis + min(r0 + min(lane, (uint32_t)VF_GM_VROWS - 1u), gm);
+        asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(ax_coord) : "l"(&pa->coord));
+        asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(az_coord) : "l"(&pz->coord));
+        if (!TMA) {
+            asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(ax_tx) : "l"(&pa->tx));
+            asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(az_ty) : "l"(&pz->ty));
         }
     };
-    VfAxis ax = {0.0f, 0.0f, 0, 0}, az = ax;
-    fetch_axes(cur, ax, az);
+    if (cur < ntasks) {
+        decode(cur, strip, j0, nr);
+        issue(true, strip, j0, 0u);
+        fetch_axes(strip, j0);
+    }
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
     float P0 = f.P[0], P5 = f.P[5], P10 = f.P[10], P11 = f.P[11], P14 = f.P[14], P15 = f.P[15];
@@ -326,22 +334,22 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     unsigned long long t_task = 0ull;
     if (dbg) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_task)); if (lane == 0) dbg[2u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5))] = t_task; }
     while (cur < ntasks) {
-        issue(nxt, stage ^ 1u);
+        uint32_t nstrip = 0u, nj0 = 0u, nnr = 0u;           // place of `nxt`
+        if (nxt < ntasks) decode(nxt, nstrip, nj0, nnr);
+        issue(nxt < ntasks, nstrip, nj0, stage ^ 1u);
         const uint32_t asked = ask_task();                  // becomes `nxt` at the end of this task
-        uint32_t strip, j0, nr;
-        decode(cur, strip, j0, nr);
         const uint32_t i = strip * VF_GM_QCOLS + lane;
         const uint32_t nrows = min(nr + 1u, f.G - j0);      // vertex rows of this task
         const bool colv = i < f.G;
         const bool cellv = lane < VF_GM_QCOLS && i + 1u < f.G;
         // ---- per-column and per-row constants ----
-        const float wx = __fmul_rn(ax.coord, f.spacing);
+        const float wx = __fmul_rn(ax_coord, f.spacing);
         const float a0 = fmaf(f.V[0], wx, f.V[12]), a1 = fmaf(f.V[1], wx, f.V[13]), a2 = fmaf(f.V[2], wx, f.V[14]);
-        const float sx25 = SHIPPED ? __fmul_rn(sinf(__fmul_rn(ax.coord, 1.3f)), 0.25f) : 0.0f;
+        const float sx25 = SHIPPED ? __fmul_rn(sinf(__fmul_rn(ax_coord, 1.3f)), 0.25f) : 0.0f;
         if (lane < VF_GM_VROWS) {
-            w.wz[lane] = __fmul_rn(az.coord, f.spacing);
-            w.ty[lane] = az.ty;
-            if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az.coord, 1.1f)), 0.25f);
+            w.wz[lane] = __fmul_rn(az_coord, f.spacing);
+            w.ty[lane] = az_ty;
+            if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az_coord, 1.1f)), 0.25f);
         }
         __syncwarp();
         unsigned long long tp0 = 0ull, tp1 = 0ull, tp2 = 0ull;
@@ -353,8 +361,8 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         float pZ = 0.0f, pZn = 0.0f;
         uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the guard band)
         const float* texel = &w.dem[stage][((strip * VF_GM_QCOLS) & 3u) + lane];
-        const float* gtexel = dem + ax.tx;
-        fetch_axes(nxt, ax, az);                            // used at the start of the next task
+        const float* gtexel = dem + ax_tx;
+        if (nxt < ntasks) fetch_axes(nstrip, nj0);          // used at the start of the next task
         const uint32_t cell0 = (j0 - 1u) * gm + i;          // cell index of (row r-1, column i) is cell0 + r*gm
         uint32_t r = 0u;
         auto load_h = [&](uint32_t rr) -> float {
@@ -514,6 +522,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             t_task = t1;
         }
         cur = nxt;
+        strip = nstrip; j0 = nj0; nr = nnr;
         nxt = got_task(asked);
         stage ^= 1u;
     }

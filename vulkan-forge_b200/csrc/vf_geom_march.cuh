@@ -32,19 +32,28 @@
 #define VF_GM_CTAS 2                         // resident CTAs per SM the register budget is set for
 #endif
 #define VF_GM_QCOLS 31                       // cell columns per task (32 vertex columns)
-#define VF_GM_ROWS 24                        // cell rows per task
+#ifndef VF_GM_ROWS_N
+#define VF_GM_ROWS_N 30                      // cell rows per task; with depth the rings carry z as well and the
+#endif
+#ifndef VF_GM_ROWS_D
+#define VF_GM_ROWS_D 26                      // staging ring gets shorter (16 warps x ~14 KB fill the SM's shared memory)
+#endif
 #define VF_GM_BOX_X 36                       // TMA box width: 32 columns + up to 3 of alignment slack
-#define VF_GM_STAGE_FLOATS 928               // 25 x 36 floats rounded up to a multiple of 128 bytes
-#define VF_GM_VROWS (VF_GM_ROWS + 1)
+template <bool DEPTH>
+struct VfGmDim {
+    static constexpr uint32_t ROWS = DEPTH ? VF_GM_ROWS_D : VF_GM_ROWS_N;     // <= 31: per-row tables are filled by lane
+    static constexpr uint32_t VROWS = ROWS + 1u;
+    static constexpr uint32_t STAGE_FLOATS = (VROWS * VF_GM_BOX_X + 31u) / 32u * 32u;   // a box, rounded up to 128 bytes
+};
 #define VF_GM_QCAP 64                        // cell ring: a row adds <= 31, rows run while <= 32 wait
 #define VF_GM_NCAP 64                        // long-triangle ring: drained in groups of 32
 
 template <bool DEPTH>
 struct VfGmWarpT {
-    alignas(128) float dem[2][VF_GM_STAGE_FLOATS];       // TMA ring: texels of the current / next task (rows of 36)
+    alignas(128) float dem[2][VfGmDim<DEPTH>::STAGE_FLOATS];   // TMA ring: texels of the current / next task (rows of 36)
     alignas(8) uint64_t mbar[2];
-    float wz[VF_GM_VROWS], kz[VF_GM_VROWS];              // per row: z*spacing, 0.25*cos(1.1 z)
-    int ty[VF_GM_VROWS];                                 // per row: texel row
+    float wz[VfGmDim<DEPTH>::VROWS], kz[VfGmDim<DEPTH>::VROWS];   // per row: z*spacing, 0.25*cos(1.1 z)
+    int ty[VfGmDim<DEPTH>::VROWS];                       // per row: texel row
     alignas(8) int2 qv[4][VF_GM_QCAP];                   // queued cells: snapped (X, Y) of a, b, c, d
     float qz[DEPTH ? 4 : 1][DEPTH ? VF_GM_QCAP : 1];     // depth only
     uint32_t qcell[VF_GM_QCAP];                          // cell index | bit 31: rebuild from scratch (clip flags mixed)
@@ -113,10 +122,18 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
                 vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
             });
 #else
-            vf_thin_raster32(es, x0, x1, y0, y1, [&](int px, int py) {
-                int64_t ed[3];
-                if (DEPTH) vf_edges_at(es, px - x0, py - y0, ed);
-                vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
+            vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](uint32_t idx, int m, int c, bool cols) {
+                float zf = 0.0f;
+                if (DEPTH) {
+                    int64_t ed[3];
+                    float b[3];
+                    vf_edges_at(es, cols ? m : c, cols ? c : m, ed);
+                    vf_edges_unbias(es, ed);
+                    vf_barycentric(ed, b);
+                    zf = vf_depth_at(t, b);
+                    if (!(zf < 1.0f)) return;
+                }
+                vf_vis_update(vis + idx, DEPTH, prim, zf);
             });
 #endif
         }
@@ -252,11 +269,12 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
 #ifndef VF_GM_PROFILE                                       // the timing dump costs registers: only in -DVF_GM_PROFILE builds
     dbg = nullptr;
 #endif
+    constexpr uint32_t VROWS = VfGmDim<DEPTH>::VROWS;
     const uint32_t lane = threadIdx.x & 31u;
     VfGmWarpT<DEPTH>& w = reinterpret_cast<VfGmWarpT<DEPTH>*>(vf_gm_smem)[threadIdx.x >> 5];
     const uint32_t gm = f.G - 1u;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1u) / VF_GM_QCOLS;
-    // A task = one strip of one row segment.  segtab[seg] = (first cell row, cell rows <= VF_GM_ROWS):
+    // A task = one strip of one row segment.  segtab[seg] = (first cell row, cell rows <= VfGmDim::ROWS):
     // the host tapers the segment height towards the end of the grid (vf_terrain.cu), and the
     // dispenser hands tasks out in order, so the short ones come last and the workers finish together.
     const uint32_t ntasks = nstrips * nsegs;
@@ -284,7 +302,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     auto got_task = [&](uint32_t t) -> uint32_t { return 2u * nworkers + (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
     auto issue = [&](bool valid, uint32_t strip, uint32_t j0, uint32_t stage) {   // lane 0: start the TMA of a task into `stage`
         if (TMA && lane == 0 && valid) {
-            vf_mbar_expect_tx(&w.mbar[stage], VF_GM_VROWS * VF_GM_BOX_X * 4u);
+            vf_mbar_expect_tx(&w.mbar[stage], VROWS * VF_GM_BOX_X * 4u);
             vf_tma_load_2d(&w.dem[stage][0], &dem_map, (int)((strip * VF_GM_QCOLS) & ~3u), (int)j0, &w.mbar[stage]);
         }
     };
@@ -308,7 +326,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     int ax_tx = 0, az_ty = 0;
     auto fetch_axes = [&](uint32_t s0, uint32_t r0) {
         const VfAxis* pa = axis + min(s0 * VF_GM_QCOLS + lane, gm);
-        const VfAxis* pz = axis + min(r0 + min(lane, (uint32_t)VF_GM_VROWS - 1u), gm);
+        const VfAxis* pz = axis + min(r0 + min(lane, VROWS - 1u), gm);
         asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(ax_coord) : "l"(&pa->coord));
         asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(az_coord) : "l"(&pz->coord));
         if (!TMA) {
@@ -346,7 +364,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         const float wx = __fmul_rn(ax_coord, f.spacing);
         const float a0 = fmaf(f.V[0], wx, f.V[12]), a1 = fmaf(f.V[1], wx, f.V[13]), a2 = fmaf(f.V[2], wx, f.V[14]);
         const float sx25 = SHIPPED ? __fmul_rn(sinf(__fmul_rn(ax_coord, 1.3f)), 0.25f) : 0.0f;
-        if (lane < VF_GM_VROWS) {
+        if (lane < VROWS) {
             w.wz[lane] = __fmul_rn(az_coord, f.spacing);
             w.ty[lane] = az_ty;
             if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az_coord, 1.1f)), 0.25f);

@@ -46,17 +46,17 @@ struct vf_scene {
     uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [2] high-water marks (pairs, queued prims)
     uint32_t* d_maxpairs = nullptr;      // = d_tile_off + n_tiles + 1
     uint2* d_segtab = nullptr;           // k_geom_march row segments (first row, rows), rebuilt when G changes
-    uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0;
+    uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
-    alignas(64) CUtensorMap dem_map_gm;  // same tensor, box 36x29 floats (k_geom_march: one box per warp task)
+    alignas(64) CUtensorMap dem_map_gm[2];  // same tensor, one box per warp task of k_geom_march: [0] 36x31 floats, [1] 36x27 (depth)
     bool use_tma = false;                // grid == DEM with identity texel mapping
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
     // front image render; swapped in by the next submit
     float* d_dem_back = nullptr;
-    alignas(64) CUtensorMap dem_map_b, dem_map_gm_b;
+    alignas(64) CUtensorMap dem_map_b, dem_map_gm_b[2];
     bool back_valid = false, back_pending = false, front_released_once = false;
     cudaStream_t upload_stream = nullptr;
     cudaEvent_t ev_uploaded = nullptr, ev_front_released = nullptr;
@@ -164,10 +164,10 @@ static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pit
     const cuuint64_t gdim[2] = {w, h};
     const cuuint64_t gstride[1] = {(cuuint64_t)pitch * 4};
     const cuuint32_t estr[2] = {1, 1};
-    const cuuint32_t boxes[2][2] = {{VF_TMA_BOX_X, VF_TMA_BOX_Y}, {VF_GM_BOX_X, VF_GM_VROWS}};
-    CUtensorMap* maps[2] = {m_tiled, m_march};
+    const cuuint32_t boxes[3][2] = {{VF_TMA_BOX_X, VF_TMA_BOX_Y}, {VF_GM_BOX_X, VfGmDim<false>::VROWS}, {VF_GM_BOX_X, VfGmDim<true>::VROWS}};
+    CUtensorMap* maps[3] = {m_tiled, m_march, m_march + 1};
     bool ok = true;
-    for (int k = 0; k < 2; ++k)
+    for (int k = 0; k < 3; ++k)
         ok = ok && tmap_encoder()(maps[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, d_dem, gdim, gstride, boxes[k], estr,
                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -197,7 +197,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     // u*W can break this near the upper end at large sizes), checked on the device
     s->use_tma = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
-    memset(&s->dem_map_gm, 0, sizeof s->dem_map_gm);
+    memset(s->dem_map_gm, 0, sizeof s->dem_map_gm);
     if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
         if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
         const uint32_t one = 1u;
@@ -207,7 +207,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
         VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (flag == 1u) {
-            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, &s->dem_map_gm);
+            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, s->dem_map_gm);
         }
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
@@ -386,12 +386,12 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
     const uint32_t per_sm = VF_GM_CTAS;     // CTAs per SM (launch bounds of k_geom_march)
     const uint32_t workers = (uint32_t)sm_count * per_sm * VF_GM_WARPS;
     uint32_t rows = (uint32_t)(((uint64_t)gm * nstrips) / (2ull * workers));
-    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), VF_GM_ROWS);
+    rows = std::min<uint32_t>(std::max<uint32_t>(rows, 1u), f.depth ? VfGmDim<true>::ROWS : VfGmDim<false>::ROWS);
     // Row segments: full height while plenty of work is left, then tapering (guided self-scheduling:
     // a task is 1/(taper x workers) of what remains) so that the last tasks handed out are short.
     static const int taper = getenv("VF_GM_TAPER") ? atoi(getenv("VF_GM_TAPER")) : 1;
     static const int min_rows = getenv("VF_GM_MIN_ROWS") ? atoi(getenv("VF_GM_MIN_ROWS")) : 4;
-    if (s->segtab_G != s->G || s->segtab_workers != workers) {
+    if (s->segtab_G != s->G || s->segtab_workers != workers || s->segtab_rows != rows) {
         std::vector<uint2> tab;
         const uint32_t lo = std::min<uint32_t>(std::max(min_rows, 1), rows);
         for (uint32_t j = 0; j < gm;) {
@@ -409,7 +409,7 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         }
         VF_CUDA(cudaStreamSynchronize(s->stream));      // frames in flight may still read the old table
         VF_CUDA(cudaMemcpy(s->d_segtab, tab.data(), tab.size() * sizeof(uint2), cudaMemcpyHostToDevice));
-        s->segtab_n = (uint32_t)tab.size(); s->segtab_G = s->G; s->segtab_workers = workers;
+        s->segtab_n = (uint32_t)tab.size(); s->segtab_G = s->G; s->segtab_workers = workers; s->segtab_rows = rows;
     }
     const uint32_t nsegs = s->segtab_n, ntasks = nstrips * nsegs;
     // the task dispenser counts in float (vf_geom_march.cuh): exact while every request stays below 2^24
@@ -430,7 +430,7 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         VF_CUDA(cudaMemsetAsync(d_dbg, 0, need * 8, s->stream));
     }
 #define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
-        f, s->dem_map_gm, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, dbg_path ? d_dbg : nullptr)
+        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, dbg_path ? d_dbg : nullptr)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
     else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }
@@ -522,7 +522,7 @@ static int scene_apply_pending_dem(vf_scene* s) {
     VF_CUDA(cudaEventRecord(s->ev_front_released, s->stream));   // every frame of the old image precedes this
     s->front_released_once = true;
     std::swap(s->d_dem, s->d_dem_back);
-    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b);
+    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
     s->back_pending = false;
     return VF_OK;
 }
@@ -599,7 +599,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 // ---- pipelined interface: uploads and batches overlap across calls -------------------------------
 static void scene_swap_images(vf_scene* s) {
     std::swap(s->d_dem, s->d_dem_back);
-    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm, s->dem_map_gm_b);
+    std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
 }
 
 // Waits for batch `id`.  If one of its kernels ran out of queue / pair space (judged against the
@@ -649,7 +649,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
         s->back_valid = false;
     }
     if (!s->back_valid) {
-        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, &s->dem_map_gm_b))
+        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, s->dem_map_gm_b))
             return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
         s->back_valid = true;
     }

@@ -159,10 +159,12 @@ __device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1,
 //                runs on wrapped 32-bit sums (one IADD per edge and step);
 //   flat edges : an edge parallel to the run (amaj == 0) is constant on a line; its exact 64-bit
 //                sign is taken once per line and it is left out of the 32-bit test.
-// emit(px, py) gets no edge values (depth: vf_edges_at on the covered sample restores them).
+// emit(idx, m, c, cols) gets the sample's index in the W-wide frame and its (line, position on the line);
+// no edge values (depth: vf_edges_at on the covered sample restores them).
 template <typename Emit>
-__device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x1, int y0, int y1, Emit&& emit) {
+__device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x1, int y0, int y1, uint32_t W, Emit&& emit) {
     const bool cols = (x1 - x0) <= (y1 - y0);        // minor axis = x: walk columns, runs along y
+    const uint32_t istep = cols ? W : 1u;
     const int nmin = cols ? x1 - x0 + 1 : y1 - y0 + 1;
     const int nmaj = cols ? y1 - y0 + 1 : x1 - x0 + 1;
     uint32_t e32[3], smin[3], smaj[3];                // low words: value at (line 0, sample 0), step per line / per sample
@@ -204,9 +206,12 @@ __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x
         uint32_t ed0 = e32[0] + smin[0] * (uint32_t)m + smaj[0] * (uint32_t)c0;
         uint32_t ed1 = e32[1] + smin[1] * (uint32_t)m + smaj[1] * (uint32_t)c0;
         uint32_t ed2 = e32[2] + smin[2] * (uint32_t)m + smaj[2] * (uint32_t)c0;
+        // sample index in the frame, stepped along the run (W per sample down a column, 1 along a row)
+        uint32_t idx = cols ? (uint32_t)(y0 + c0) * W + (uint32_t)(x0 + m) : (uint32_t)(y0 + m) * W + (uint32_t)(x0 + c0);
         for (int c = c0; c <= c1; ++c) {
-            if ((int32_t)(ed0 | ed1 | ed2) >= 0) emit(cols ? x0 + m : x0 + c, cols ? y0 + c : y0 + m);
+            if ((int32_t)(ed0 | ed1 | ed2) >= 0) emit(idx, m, c, cols);
             ed0 += smaj[0]; ed1 += smaj[1]; ed2 += smaj[2];
+            idx += istep;
         }
     }
 }

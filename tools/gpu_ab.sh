@@ -11,3 +11,7 @@ timeout 300 python tools/profile_frame.py 8 2>&1 | tee $OUT/profile_frame.log
 if [ -n "$2" ]; then
   timeout $(( $2 + 120 )) python tools/fuzz_parity.py $2 ${3:-201} 2>&1 | tail -8 | tee $OUT/fuzz.log
 fi
+if [ -n "$4" ]; then
+  timeout $(( $4 + 120 )) python tools/fuzz_parity.py api $4 ${3:-201} 2>&1 | tail -4 | tee $OUT/fuzz_api.log
+  VF_TEST_SMALL_BUFFERS=1 timeout $(( $4 + 120 )) python tools/fuzz_parity.py api $4 ${3:-201} 2>&1 | tail -4 | tee -a $OUT/fuzz_api.log
+fi

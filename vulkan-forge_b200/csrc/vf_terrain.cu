@@ -66,11 +66,17 @@ struct vf_scene {
         cudaEvent_t done = nullptr; bool busy = false; std::vector<float> u; int n = 0; uint8_t* out = nullptr;
         // state of the scene when the batch was submitted: an overflow is judged against THESE capacities
         // (a later batch may have grown the buffers since) and the batch is redone from THIS height image
-        uint32_t cap_pairs = 0, cap_big = 0; const float* dem = nullptr;
+        uint32_t cap_pairs = 0, cap_big = 0; const float* dem = nullptr; bool skipped_bins = false;
         int mode = 0, depth = 0; float h_min = 0.0f, h_max = 0.0f;
         bool resolved = false; int rc = 0;
     };
     Ticket tickets[4];
+    // Speculative binning: frames of a terrain seen whole queue nothing for the sort-middle stage, and the
+    // launch of k_binsort alone costs 6 us (3 % of a 1080p frame), so it is left out until a frame does
+    // queue something (k_raster reports it in high_water[2]); that frame / batch is rendered again with
+    // the stage in place, which then stays for bin_hold frames (doubling each time it proves necessary).
+    uint32_t bin_hold = 0, bin_hold_len = 32;
+    bool submit_skipped_bins = false;
     bool slot_used[2] = {false, false};
     uint32_t* d_flag = nullptr;
     uint32_t* d_tile_cursor = nullptr;   // [n_tiles]
@@ -476,7 +482,11 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
-    {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
+    static const bool bin_always = getenv("VF_BIN_ALWAYS") != nullptr;
+    if (s->bin_hold == 0 && !bin_always) {
+        s->submit_skipped_bins = true;
+    } else {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
+        if (s->bin_hold) --s->bin_hold;
         static int binsort_ctas = 0;
         if (!binsort_ctas) {
             int dev = 0, sms = 0, per_sm = 0;
@@ -493,7 +503,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
     k_raster<<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
-                                                s->d_sorted, s->d_counters, clear, frame, d_vis);
+                                                s->d_sorted, s->d_counters, clear, frame, d_vis, s->d_maxpairs);
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());
     return VF_OK;
@@ -536,6 +546,7 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
     if (rc) return rc;
     const size_t fbytes = (size_t)s->W * s->H * 4;
     VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
+    s->submit_skipped_bins = false;
     for (int k = 0; k < n; ++k) {
         const int slot = k % VF_MAX_SLOTS;
         if (out_host && s->slot_used[slot]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
@@ -558,10 +569,15 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 
 // after the batch of pinned slot `hslot` has completed: 0 = fine, 1 = a buffer overflowed and was
 // grown (the batch must be rendered again), < 0 = error code
-static int scene_check_overflow(vf_scene* s, int hslot) {
+static int scene_check_overflow(vf_scene* s, int hslot, bool skipped_bins) {
     const uint32_t* h = s->h_counters + (size_t)hslot * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
-    const uint32_t need = h[0], need_big = h[1];
-    if (need <= s->capacity && need_big <= s->big_capacity) return 0;
+    const uint32_t need = h[0], need_big = std::max(h[1], h[2]);
+    if (h[2] > 0) {                                      // a frame queued primitives: keep the binning stage for a while
+        if (skipped_bins) s->bin_hold_len = std::min<uint32_t>(s->bin_hold_len * 2u, 1u << 20);
+        s->bin_hold = s->bin_hold_len;
+    }
+    const bool redo_bins = skipped_bins && h[2] > 0;
+    if (need <= s->capacity && need_big <= s->big_capacity) return redo_bins ? 1 : 0;
     VF_CUDA(cudaStreamSynchronize(s->stream));           // nothing in flight may still use the buffers
     if (need > (1u << 30)) return -vf_set_error(VF_E_OOM, "binning needs %u pairs (limit 2^30)", need);
     int rc;
@@ -589,7 +605,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
         memcpy(s->h_counters_last, s->h_counters, VF_CNT_WORDS * 4);
-        const int ov = scene_check_overflow(s, 0);
+        const int ov = scene_check_overflow(s, 0, s->submit_skipped_bins);
         if (ov < 0) return -ov;
         if (ov == 0) return scene_finish_stats(s);
     }
@@ -613,8 +629,11 @@ static int ticket_resolve(vf_scene* s, int id) {
     t.rc = VF_OK;
     if (cudaEventSynchronize(t.done) != cudaSuccess) return t.rc = vf_set_error(VF_E_CUDA, "batch %d: %s", id, cudaGetErrorString(cudaGetLastError()));
     const uint32_t* h = s->h_counters + (size_t)(1 + id) * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
-    if (h[0] <= t.cap_pairs && h[1] <= t.cap_big) return VF_OK;
-    const int ov = scene_check_overflow(s, 1 + id);       // grows what is still too small (a later batch may have done it already)
+    if (h[0] <= t.cap_pairs && std::max(h[1], h[2]) <= t.cap_big && !(t.skipped_bins && h[2] > 0)) {
+        if (h[2] > 0) s->bin_hold = s->bin_hold_len;
+        return VF_OK;
+    }
+    const int ov = scene_check_overflow(s, 1 + id, t.skipped_bins);   // grows what is still too small (a later batch may have done it already)
     if (ov < 0) return t.rc = -ov;
     const bool other = t.dem != s->d_dem;
     if (other && (t.dem != s->d_dem_back || s->back_pending))
@@ -676,6 +695,7 @@ extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int 
     rc = scene_submit(s, u44xn, n, out_rgba_host, nullptr, 1 + id);
     if (rc) return rc;
     t.cap_pairs = s->capacity; t.cap_big = s->big_capacity; t.dem = s->d_dem;       // after the swap inside scene_submit
+    t.skipped_bins = s->submit_skipped_bins;
     t.mode = s->mode; t.depth = s->depth; t.h_min = s->h_min; t.h_max = s->h_max;
     t.resolved = false; t.rc = VF_OK;
     // done = counters read back on the render stream and every frame copied on the copy stream

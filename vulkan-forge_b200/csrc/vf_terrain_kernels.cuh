@@ -581,10 +581,16 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
          const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,
          const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ sorted_prim,
          const uint32_t* __restrict__ counters, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba,
-         uint32_t* __restrict__ out_vis) {
+         uint32_t* __restrict__ out_vis, uint32_t* __restrict__ high_water) {
     __shared__ unsigned long long s_key[VF_TILE * VF_TILE];
     __shared__ float s_thr[256];
     const uint32_t tid = threadIdx.x;
+    // high_water[2]: most primitives any frame of the batch queued for binning.  The host launches k_binsort
+    // speculatively NOT at all while frames queue nothing (vf_terrain.cu); this is how it learns otherwise.
+    if ((blockIdx.x | blockIdx.y | tid) == 0u) {
+        const uint32_t nbig = counters[VF_CNT_BIG];
+        if (nbig) atomicMax(&high_water[2], nbig);
+    }
     const uint32_t tyi = blockIdx.y, txi = blockIdx.x;      // grid = tiles_x x tiles_y
     const uint32_t tile = tyi * f.tiles_x + txi;
     const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;

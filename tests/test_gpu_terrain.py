@@ -92,6 +92,37 @@ def test_near_plane_clipping_path(ext, oracle, luts, synthetic_dem):
         _check(got, ref, gvis, rvis, mode)
 
 
+def test_speculative_binning_redo(ext, vf, oracle, luts, synthetic_dem):
+    """k_binsort is launched only once a frame has queued primitives for it: a scene seen whole skips the
+    stage, the first close-up is detected (k_raster reports the queue) and rendered again with the stage,
+    also inside a batch whose first frames needed nothing.  Every frame equals the oracle's."""
+    W, H, G = 320, 200, 64
+    dem = synthetic_dem(6, 64) * np.float32(0.2)
+    far = ((3.0, 2.0, 3.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 45.0, 0.1, 100.0)
+    near = ((0.0, 0.15, 0.0), (1.0, 0.0, 1.0), (0.0, 1.0, 0.0), 90.0, 0.1, 100.0)
+    sc = ext.Scene(W, H, grid=G, colormap="viridis")
+    sc.set_height_from_r32f(dem)
+    sc.set_shading("northstar", depth=True)
+    lo, hi = sc.set_auto_height_range()
+
+    def ref(cam):
+        sc.set_camera_look_at(*cam)
+        return oracle.render_terrain(W, H, G, dem, sc.debug_uniforms_f32(), luts["viridis"], mode=oracle.MODE_NORTHSTAR,
+                                     depth=True, h_min=float(lo), h_max=float(hi))
+    r_far, r_near = ref(far), ref(near)
+    for cam, want, bins in ((far, r_far, False), (near, r_near, True), (far, r_far, False), (near, r_near, True)):
+        sc.set_camera_look_at(*cam)
+        assert np.array_equal(sc.render_rgba(), want)
+        assert (sc.render_metrics()["big_prims"] > 0) == bins
+    fresh = ext.Scene(W, H, grid=G, colormap="viridis")                # batch: two quiet frames, then the close-up
+    fresh.set_height_from_r32f(dem)
+    fresh.set_shading("northstar", depth=True)
+    fresh.set_height_range(lo, hi)
+    batch = fresh.render_batch_rgba([far, far, near, far])
+    for k, want in enumerate((r_far, r_far, r_near, r_far)):
+        assert np.array_equal(batch[k], want), k
+
+
 def _correct_projection_uniforms(oracle, W, H, eye, tgt, fovy, zn, zf):
     """The shipped gl_to_wgpu is transposed (src/camera.rs:14-21), which makes z <= w always true, so
     the far plane can only be reached with a correct [0,1]-depth projection supplied as raw uniforms."""

@@ -200,16 +200,22 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                             nbias |= tl ? 0u : (1u << i);
                             E[i] = A[i] * (sx - a.X) + B[i] * (sy - a.Y) - (tl ? 0 : 1);
                         }
-                        for (int dy = 0; dy < bh; ++dy)
-                            for (int dx = 0; dx < bw; ++dx) {
-                                const int32_t e0 = E[0] + A[0] * (dx * VF_SUBPIX) + B[0] * (dy * VF_SUBPIX);
-                                const int32_t e1 = E[1] + A[1] * (dx * VF_SUBPIX) + B[1] * (dy * VF_SUBPIX);
-                                const int32_t e2 = E[2] + A[2] * (dx * VF_SUBPIX) + B[2] * (dy * VF_SUBPIX);
-                                if ((e0 | e1 | e2) >= 0) {
-                                    int64_t ed[3] = {e0, e1, e2};
-                                    vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
-                                }
+                        // the (at most four) samples in one loop: along the row, then down to the next one
+                        int32_t e0 = E[0], e1 = E[1], e2 = E[2];
+                        const int32_t a0 = A[0] * VF_SUBPIX, a1 = A[1] * VF_SUBPIX, a2 = A[2] * VF_SUBPIX;
+                        const int32_t r0 = B[0] * VF_SUBPIX - (bw - 1) * a0, r1 = B[1] * VF_SUBPIX - (bw - 1) * a1,
+                                      r2 = B[2] * VF_SUBPIX - (bw - 1) * a2;
+                        int dx = 0, dy = 0;
+                        for (int n = 0; n < npx; ++n) {
+                            if ((e0 | e1 | e2) >= 0) {
+                                int64_t ed[3] = {e0, e1, e2};
+                                vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
                             }
+                            const bool wrap = dx + 1 == bw;
+                            e0 += wrap ? r0 : a0; e1 += wrap ? r1 : a1; e2 += wrap ? r2 : a2;
+                            dx = wrap ? 0 : dx + 1;
+                            dy += wrap ? 1 : 0;
+                        }
                     } else if (vf_serial_ok(t, bw, bh)) {
                         to_long = true;
                     } else {

@@ -293,7 +293,7 @@ def main():
             "mpix_per_s": fps * W * H / 1e6,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},
-            "gpu_launches": args.steps * F * 3,   # k_geom_march, k_binsort, k_raster per frame (value leg)
+            "gpu_launches": args.steps * F * 2,   # k_geom_march + k_raster per frame (value leg); k_binsort is not launched while frames queue nothing for it
             "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_raster"}[dom],
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic({"ms_geom": "k_geom", "ms_bin": "k_bin", "ms_raster": "k_raster"}[dom]),

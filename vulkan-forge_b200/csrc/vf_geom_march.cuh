@@ -291,6 +291,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         j0 = e.x; nr = e.y;
     };
     const uint32_t below = (1u << lane) - 1u;
+    const uint32_t qv_base = vf_smem_u32(&w.qv[0][0]), qcell_base = vf_smem_u32(&w.qcell[0]);
 
     // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
     // The counter is kept as a FLOAT (exact below 2^24 tasks; the host falls back to more rows per task
@@ -411,17 +412,19 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             Y = __float2int_rn(fmaf(-yn, hh, hh));
             Z = DEPTH ? __fmul_rn(c[2], invw) : 0.0f;
         };
+        // Branch-free: every lane computes a slot, the stores are predicated (asm: the compiler would put
+        // the five stores behind a divergent branch, and branch resolution is a sixth of this kernel's stalls).
+        static_assert(VF_GM_QCAP * sizeof(int2) == 512, "offsets of the predicated stores below");
         auto append = [&](uint32_t m, bool keep, uint32_t cell, int32_t aX, int32_t aY, float aZ, int32_t bX, int32_t bY, float bZ,
                           int32_t cX, int32_t cY, float cZ, int32_t dX, int32_t dY, float dZ) {
-            if (keep) {
-                const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
-                w.qv[0][s] = make_int2(aX, aY);
-                w.qv[1][s] = make_int2(bX, bY);
-                w.qv[2][s] = make_int2(cX, cY);
-                w.qv[3][s] = make_int2(dX, dY);
-                if (DEPTH) { w.qz[0][s] = aZ; w.qz[1][s] = bZ; w.qz[2][s] = cZ; w.qz[3][s] = dZ; }
-                w.qcell[s] = cell;
-            }
+            const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t"
+                         "@p st.shared.v2.b32 [%1], {%3, %4};\n\t@p st.shared.v2.b32 [%1+512], {%5, %6};\n\t"
+                         "@p st.shared.v2.b32 [%1+1024], {%7, %8};\n\t@p st.shared.v2.b32 [%1+1536], {%9, %10};\n\t"
+                         "@p st.shared.b32 [%2], %11;\n\t}"
+                         :: "r"((uint32_t)keep), "r"(qv_base + s * 8u), "r"(qcell_base + s * 4u), "r"(aX), "r"(aY), "r"(bX), "r"(bY),
+                            "r"(cX), "r"(cY), "r"(dX), "r"(dY), "r"(cell) : "memory");
+            if (DEPTH && keep) { w.qz[0][s] = aZ; w.qz[1][s] = bZ; w.qz[2][s] = cZ; w.qz[3][s] = dZ; }
             q.qn += (uint32_t)__popc(m);
         };
 
@@ -456,7 +459,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             }
             pst = st; pstn = stn; pnin = nin;
             const uint32_t m = __ballot_sync(0xffffffffu, keep);
-            if (m) append(m, keep, (cell0 + r * gm) | rebuild, pX, pY, pZ, pXn, pYn, pZn, X, Y, Z, Xn, Yn, Zn);
+            append(m, keep, (cell0 + r * gm) | rebuild, pX, pY, pZ, pXn, pYn, pZn, X, Y, Z, Xn, Yn, Zn);
             pX = X; pY = Y; pXn = Xn; pYn = Yn; pZ = Z; pZn = Zn;
             ++r;
         };
@@ -495,13 +498,13 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
                 vf_span_has_centre(min(min(XB, XBn), eAx0), max(max(XB, XBn), eAx1)) &
                 vf_span_has_centre(min(min(YB, YBn), eAy0), max(max(YB, YBn), eAy1));
             const uint32_t mA = __ballot_sync(0xffffffffu, keepA), mB = __ballot_sync(0xffffffffu, keepB);
-            if (mA) append(mA, keepA, cell0 + r * gm, pX, pY, pZ, pXn, pYn, pZn, XA, YA, ZA, XAn, YAn, ZAn);
+            append(mA, keepA, cell0 + r * gm, pX, pY, pZ, pXn, pYn, pZn, XA, YA, ZA, XAn, YAn, ZAn);
             if (q.qn + (uint32_t)__popc(mB) > VF_GM_QCAP) {      // ring full (coarse grids): row B is redone after the drain
                 pX = XA; pY = YA; pXn = XAn; pYn = YAn; pZ = ZA; pZn = ZAn;
                 r += 1u;
                 return true;
             }
-            if (mB) append(mB, keepB, cell0 + (r + 1u) * gm, XA, YA, ZA, XAn, YAn, ZAn, XB, YB, ZB, XBn, YBn, ZBn);
+            append(mB, keepB, cell0 + (r + 1u) * gm, XA, YA, ZA, XAn, YAn, ZAn, XB, YB, ZB, XBn, YBn, ZBn);
             pX = XB; pY = YB; pXn = XBn; pYn = YBn; pZ = ZB; pZn = ZBn;
             r += 2u;
             return true;

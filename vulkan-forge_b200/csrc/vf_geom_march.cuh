@@ -122,7 +122,9 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
                 vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
             });
 #else
-            vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](uint32_t idx, int m, int c, bool cols) {
+            vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](bool covered, uint32_t idx, int m, int c, bool cols) {
+                if (!DEPTH) { vf_vis_max_if(covered, vis + idx, prim); return; }
+                if (!covered) return;
                 float zf = 0.0f;
                 if (DEPTH) {
                     int64_t ed[3];
@@ -206,13 +208,19 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                         const int32_t r0 = B[0] * VF_SUBPIX - (bw - 1) * a0, r1 = B[1] * VF_SUBPIX - (bw - 1) * a1,
                                       r2 = B[2] * VF_SUBPIX - (bw - 1) * a2;
                         int dx = 0, dy = 0;
+                        uint32_t idx = (uint32_t)y0 * f.W + (uint32_t)x0;       // sample index in the frame
+                        const uint32_t idx_wrap = f.W - (uint32_t)(bw - 1);
                         for (int n = 0; n < npx; ++n) {
-                            if ((e0 | e1 | e2) >= 0) {
+                            const bool covered = (e0 | e1 | e2) >= 0;
+                            if (!DEPTH) {
+                                vf_vis_max_if(covered, vis + idx, prim);
+                            } else if (covered) {
                                 int64_t ed[3] = {e0, e1, e2};
                                 vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
                             }
                             const bool wrap = dx + 1 == bw;
                             e0 += wrap ? r0 : a0; e1 += wrap ? r1 : a1; e2 += wrap ? r2 : a2;
+                            idx += wrap ? idx_wrap : 1u;
                             dx = wrap ? 0 : dx + 1;
                             dy += wrap ? 1 : 0;
                         }
@@ -227,15 +235,17 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
         q.qhead = (q.qhead + take) & (VF_GM_QCAP - 1u);
         q.qn -= take;
         const uint32_t nm = __ballot_sync(0xffffffffu, to_long);
-        if (nm) {
-            if (to_long) {
-                const uint32_t s = (q.nhead + q.nn + __popc(nm & below)) & (VF_GM_NCAP - 1u);
+        {   // branch-free append to the ring of long triangles (predicated stores, as in the march)
+            static_assert(VF_GM_NCAP * sizeof(int2) == 512, "offsets of the predicated stores below");
+            const uint32_t s = (q.nhead + q.nn + __popc(nm & below)) & (VF_GM_NCAP - 1u);
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t"
+                         "@p st.shared.v2.b32 [%1], {%3, %4};\n\t@p st.shared.v2.b32 [%1+512], {%5, %6};\n\t"
+                         "@p st.shared.v2.b32 [%1+1024], {%7, %8};\n\t@p st.shared.b32 [%2], %9;\n\t}"
+                         :: "r"((uint32_t)to_long), "r"(vf_smem_u32(&w.nv[0][0]) + s * 8u), "r"(vf_smem_u32(&w.nprim[0]) + s * 4u),
+                            "r"(t.v[0].X), "r"(t.v[0].Y), "r"(t.v[1].X), "r"(t.v[1].Y), "r"(t.v[2].X), "r"(t.v[2].Y), "r"(prim) : "memory");
+            if (DEPTH && to_long) {
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    w.nv[k][s] = make_int2(t.v[k].X, t.v[k].Y);
-                    if (DEPTH) w.nz[k][s] = t.v[k].zn;
-                }
-                w.nprim[s] = prim;
+                for (int k = 0; k < 3; ++k) w.nz[k][s] = t.v[k].zn;
             }
             q.nn += (uint32_t)__popc(nm);
         }

@@ -92,6 +92,11 @@ __device__ __forceinline__ void vf_prim_vertices(const VfFrame& f, const VfAxis*
     for (int k = 0; k < 3; ++k) vf_grid_vertex(f, axis, dem, ij[k][0], ij[k][1], tri[k]);
 }
 
+// no-depth resolve of a sample as one predicated reduction (no branch around it)
+__device__ __forceinline__ void vf_vis_max_if(bool covered, unsigned long long* key64, uint32_t prim) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p red.global.max.u32 [%1], %2;\n\t}"
+                 :: "r"((uint32_t)covered), "l"(key64), "r"(prim + 1u) : "memory");      // low word (little endian)
+}
 // visibility resolve on one sample (global or shared memory)
 __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool depth, uint32_t prim, float zf) {
     if (depth) atomicMin(key64, ((unsigned long long)__float_as_uint(zf) << 32) | prim);
@@ -159,7 +164,8 @@ __device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1,
 //                runs on wrapped 32-bit sums (one IADD per edge and step);
 //   flat edges : an edge parallel to the run (amaj == 0) is constant on a line; its exact 64-bit
 //                sign is taken once per line and it is left out of the 32-bit test.
-// emit(idx, m, c, cols) gets the sample's index in the W-wide frame and its (line, position on the line);
+// emit(covered, idx, m, c, cols) is called for EVERY sample of a run (so that it can be a predicated store
+// instead of a branch) with the sample's index in the W-wide frame and its (line, position on the line);
 // no edge values (depth: vf_edges_at on the covered sample restores them).
 template <typename Emit>
 __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x1, int y0, int y1, uint32_t W, Emit&& emit) {
@@ -201,17 +207,19 @@ __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x
                     dead = dead || s.E[i] + (int64_t)(cols ? s.A[i] : s.B[i]) * (int64_t)(m * VF_SUBPIX) < 0;
             if (dead) continue;
         }
-        if (!(lo <= hi)) continue;
+        // (an empty run has c0 > c1; a sample tested in vain could not hurt: the test is exact)
         const int c0 = __float2int_ru(lo), c1 = __float2int_rd(hi);      // 0 <= lo, hi <= nmaj - 1
         uint32_t ed0 = e32[0] + smin[0] * (uint32_t)m + smaj[0] * (uint32_t)c0;
         uint32_t ed1 = e32[1] + smin[1] * (uint32_t)m + smaj[1] * (uint32_t)c0;
         uint32_t ed2 = e32[2] + smin[2] * (uint32_t)m + smaj[2] * (uint32_t)c0;
         // sample index in the frame, stepped along the run (W per sample down a column, 1 along a row)
         uint32_t idx = cols ? (uint32_t)(y0 + c0) * W + (uint32_t)(x0 + m) : (uint32_t)(y0 + m) * W + (uint32_t)(x0 + c0);
-        for (int c = c0; c <= c1; ++c) {
-            if ((int32_t)(ed0 | ed1 | ed2) >= 0) emit(idx, m, c, cols);
+        int c = c0;
+        emit(c <= c1 && (int32_t)(ed0 | ed1 | ed2) >= 0, idx, m, c, cols);       // most runs hold one sample or none: no branch
+        while (++c <= c1) {
             ed0 += smaj[0]; ed1 += smaj[1]; ed2 += smaj[2];
             idx += istep;
+            emit((int32_t)(ed0 | ed1 | ed2) >= 0, idx, m, c, cols);
         }
     }
 }

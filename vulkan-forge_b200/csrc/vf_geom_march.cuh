@@ -178,56 +178,62 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                 t.v[2].X = v2.x; t.v[2].Y = v2.y;
                 if (DEPTH) { t.v[0].zn = w.qz[i0][slot]; t.v[1].zn = w.qz[2][slot]; t.v[2].zn = w.qz[i2][slot]; }
             }
-            if (st == 2) {
-                to_big = true;                           // needs clipping
-            } else if (st == 1) {
-                int x0, x1, y0, y1;
-                const int32_t mnx = min(t.v[0].X, min(t.v[1].X, t.v[2].X)), mxx = max(t.v[0].X, max(t.v[1].X, t.v[2].X));
-                const int32_t mny = min(t.v[0].Y, min(t.v[1].Y, t.v[2].Y)), mxy = max(t.v[0].Y, max(t.v[1].Y, t.v[2].Y));
-                if (vf_bbox_pixels(mnx, mxx, mny, mxy, f.W, f.H, x0, x1, y0, y1) && vf_area2(t) < 0) {
-                    const int bw = x1 - x0 + 1, bh = y1 - y0 + 1, npx = bw * bh;
-                    // Micro triangle that is small itself (not a large one with a few on-screen samples): its
-                    // extent is below 2^12 sub-pixels, the reference centre lies inside its bbox, so every
-                    // edge value stays below 2^26 and the coverage test runs in 32 bits.
-                    if (npx <= VF_MICRO_MAX && (uint32_t)((mxx - mnx) | (mxy - mny)) < 4096u) {
-                        const int32_t sx = x0 * VF_SUBPIX + VF_HALFPIX, sy = y0 * VF_SUBPIX + VF_HALFPIX;
-                        int32_t A[3], B[3], E[3];
-                        uint32_t nbias = 0u;
+            // Classification and micro coverage in straight-line code: a divergent region costs the warp its
+            // instructions whatever the number of lanes inside, so the set-up runs for every lane and only
+            // the visibility updates are predicated (branch resolution was a sixth of this kernel's stalls).
+            int x0, x1, y0, y1;
+            const int32_t mnx = min(t.v[0].X, min(t.v[1].X, t.v[2].X)), mxx = max(t.v[0].X, max(t.v[1].X, t.v[2].X));
+            const int32_t mny = min(t.v[0].Y, min(t.v[1].Y, t.v[2].Y)), mxy = max(t.v[0].Y, max(t.v[1].Y, t.v[2].Y));
+            const bool inside = vf_bbox_pixels(mnx, mxx, mny, mxy, f.W, f.H, x0, x1, y0, y1);
+            const int64_t area2 = vf_area2(t);
+            const bool ok = st == 1 && inside && area2 < 0;
+            const int bw = x1 - x0 + 1, bh = y1 - y0 + 1, npx = bw * bh;
+            // Micro triangle that is small itself (not a large one with a few on-screen samples): its extent
+            // is below 2^12 sub-pixels, the reference centre lies inside its bbox, so every edge value stays
+            // below 2^26 and the coverage test runs in 32 bits (unsigned products: other lanes may wrap).
+            const bool micro = ok && npx <= VF_MICRO_MAX && (((uint32_t)mxx - (uint32_t)mnx) | ((uint32_t)mxy - (uint32_t)mny)) < 4096u;
+            const bool serial = min(bw, bh) <= VF_SERIAL_LINES && (-area2 >> 17) <= (int64_t)VF_SERIAL_AREA;   // vf_serial_ok
+            to_long = ok && !micro && serial;
+            to_big = st == 2 || (ok && !micro && !serial);
+            const int32_t sx = x0 * VF_SUBPIX + VF_HALFPIX, sy = y0 * VF_SUBPIX + VF_HALFPIX;
+            int32_t A[3], B[3], E[3];
+            uint32_t nbias = 0u;
 #pragma unroll
-                        for (int i = 0; i < 3; ++i) {           // vf_edges_setup in 32 bits
-                            const VfSVtx& a = t.v[(i + 1) % 3];
-                            const VfSVtx& b = t.v[(i + 2) % 3];
-                            A[i] = b.Y - a.Y; B[i] = a.X - b.X;
-                            const bool tl = vf_top_left(a, b);
-                            nbias |= tl ? 0u : (1u << i);
-                            E[i] = A[i] * (sx - a.X) + B[i] * (sy - a.Y) - (tl ? 0 : 1);
-                        }
-                        // the (at most four) samples in one loop: along the row, then down to the next one
-                        int32_t e0 = E[0], e1 = E[1], e2 = E[2];
-                        const int32_t a0 = A[0] * VF_SUBPIX, a1 = A[1] * VF_SUBPIX, a2 = A[2] * VF_SUBPIX;
-                        const int32_t r0 = B[0] * VF_SUBPIX - (bw - 1) * a0, r1 = B[1] * VF_SUBPIX - (bw - 1) * a1,
-                                      r2 = B[2] * VF_SUBPIX - (bw - 1) * a2;
-                        int dx = 0, dy = 0;
-                        uint32_t idx = (uint32_t)y0 * f.W + (uint32_t)x0;       // sample index in the frame
-                        const uint32_t idx_wrap = f.W - (uint32_t)(bw - 1);
-                        for (int n = 0; n < npx; ++n) {
-                            const bool covered = (e0 | e1 | e2) >= 0;
-                            if (!DEPTH) {
-                                vf_vis_max_if(covered, vis + idx, prim);
-                            } else if (covered) {
-                                int64_t ed[3] = {e0, e1, e2};
-                                vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
-                            }
-                            const bool wrap = dx + 1 == bw;
-                            e0 += wrap ? r0 : a0; e1 += wrap ? r1 : a1; e2 += wrap ? r2 : a2;
-                            idx += wrap ? idx_wrap : 1u;
-                            dx = wrap ? 0 : dx + 1;
-                            dy += wrap ? 1 : 0;
-                        }
-                    } else if (vf_serial_ok(t, bw, bh)) {
-                        to_long = true;
-                    } else {
-                        to_big = true;
+            for (int i = 0; i < 3; ++i) {                   // vf_edges_setup in 32 bits
+                const VfSVtx& a = t.v[(i + 1) % 3];
+                const VfSVtx& b = t.v[(i + 2) % 3];
+                A[i] = b.Y - a.Y; B[i] = a.X - b.X;
+                const bool tl = vf_top_left(a, b);
+                nbias |= tl ? 0u : (1u << i);
+                E[i] = (int32_t)((uint32_t)A[i] * (uint32_t)(sx - a.X) + (uint32_t)B[i] * (uint32_t)(sy - a.Y)) - (tl ? 0 : 1);
+            }
+            // the (at most four) samples: the first one without a loop, the others along the row, then down
+            int32_t e0 = E[0], e1 = E[1], e2 = E[2];
+            uint32_t idx = (uint32_t)y0 * f.W + (uint32_t)x0;                   // sample index in the frame
+            if (!DEPTH) {
+                vf_vis_max_if(micro && (e0 | e1 | e2) >= 0, vis + idx, prim);
+            } else if (micro && (e0 | e1 | e2) >= 0) {
+                int64_t ed[3] = {e0, e1, e2};
+                vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0, y0, ed);
+            }
+            if (micro && npx > 1) {
+                const int32_t a0 = A[0] * VF_SUBPIX, a1 = A[1] * VF_SUBPIX, a2 = A[2] * VF_SUBPIX;
+                const int32_t r0 = B[0] * VF_SUBPIX - (bw - 1) * a0, r1 = B[1] * VF_SUBPIX - (bw - 1) * a1,
+                              r2 = B[2] * VF_SUBPIX - (bw - 1) * a2;
+                const uint32_t idx_wrap = f.W - (uint32_t)(bw - 1);
+                int dx = 0, dy = 0;
+                for (int n = 1; n < npx; ++n) {
+                    const bool wrap = dx + 1 == bw;
+                    e0 += wrap ? r0 : a0; e1 += wrap ? r1 : a1; e2 += wrap ? r2 : a2;
+                    idx += wrap ? idx_wrap : 1u;
+                    dx = wrap ? 0 : dx + 1;
+                    dy += wrap ? 1 : 0;
+                    const bool covered = (e0 | e1 | e2) >= 0;
+                    if (!DEPTH) {
+                        vf_vis_max_if(covered, vis + idx, prim);
+                    } else if (covered) {
+                        int64_t ed[3] = {e0, e1, e2};
+                        vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
                     }
                 }
             }
@@ -369,6 +375,12 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     unsigned long long t_task = 0ull;
     if (dbg) { asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_task)); if (lane == 0) dbg[2u * (blockIdx.x * VF_GM_WARPS + (threadIdx.x >> 5))] = t_task; }
     while (cur < ntasks) {
+        // The axis entries fetched during the previous task are consumed BEFORE this task's requests go out
+        // (asm volatile keeps the order): issued after them, their first use shares a scoreboard with the new
+        // long-latency operations and waits for those round trips (4 % of the kernel's stall samples).
+        float wx, wz_lane;
+        asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(wx) : "f"(ax_coord), "f"(f.spacing));
+        asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(wz_lane) : "f"(az_coord), "f"(f.spacing));
         uint32_t nstrip = 0u, nj0 = 0u, nnr = 0u;           // place of `nxt`
         if (nxt < ntasks) decode(nxt, nstrip, nj0, nnr);
         issue(nxt < ntasks, nstrip, nj0, stage ^ 1u);
@@ -378,11 +390,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         const bool colv = i < f.G;
         const bool cellv = lane < VF_GM_QCOLS && i + 1u < f.G;
         // ---- per-column and per-row constants ----
-        const float wx = __fmul_rn(ax_coord, f.spacing);
         const float a0 = fmaf(f.V[0], wx, f.V[12]), a1 = fmaf(f.V[1], wx, f.V[13]), a2 = fmaf(f.V[2], wx, f.V[14]);
         const float sx25 = SHIPPED ? __fmul_rn(sinf(__fmul_rn(ax_coord, 1.3f)), 0.25f) : 0.0f;
         if (lane < VROWS) {
-            w.wz[lane] = __fmul_rn(az_coord, f.spacing);
+            w.wz[lane] = wz_lane;
             w.ty[lane] = az_ty;
             if (SHIPPED) w.kz[lane] = __fmul_rn(cosf(__fmul_rn(az_coord, 1.1f)), 0.25f);
         }

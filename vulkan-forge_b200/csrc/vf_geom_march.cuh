@@ -424,6 +424,42 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             c[0] = __fmul_rn(P0, v0); c[1] = __fmul_rn(P5, v1);
             c[2] = __fadd_rn(P14, __fmul_rn(P10, v2)); c[3] = __fadd_rn(P15, __fmul_rn(P11, v2));
         };
+        // The same for two rows at once in packed f32x2 arithmetic (FFMA2 / FMUL2 / FADD2 of sm_100: one
+        // instruction per pair, IEEE round-to-nearest in each half, so the results are those of clip_pos).
+        auto pk = [](float lo, float hi) -> unsigned long long {
+            unsigned long long r;
+            asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+            return r;
+        };
+        auto fma2 = [](unsigned long long a, unsigned long long b, unsigned long long c) -> unsigned long long {
+            unsigned long long r;
+            asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+            return r;
+        };
+        auto mul2 = [](unsigned long long a, unsigned long long b) -> unsigned long long {
+            unsigned long long r;
+            asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+            return r;
+        };
+        auto clip_pos2 = [&](uint32_t rr, float ca[4], float cb[4]) {
+            if (SHIPPED) { clip_pos(rr, load_h(rr), ca); clip_pos(rr + 1u, load_h(rr + 1u), cb); return; }
+            const unsigned long long wy = mul2(pk(load_h(rr), load_h(rr + 1u)), pk(exag, exag));
+            const unsigned long long wz = pk(w.wz[rr], w.wz[rr + 1u]);
+            const unsigned long long v0 = fma2(pk(V4, V4), wy, fma2(pk(V8, V8), wz, pk(a0, a0)));
+            const unsigned long long v1 = fma2(pk(V5, V5), wy, fma2(pk(V9, V9), wz, pk(a1, a1)));
+            const unsigned long long v2 = fma2(pk(V6, V6), wy, fma2(pk(V10, V10), wz, pk(a2, a2)));
+            const unsigned long long c0 = mul2(pk(P0, P0), v0), c1 = mul2(pk(P5, P5), v1);
+            // (the additions stay scalar: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2, which
+            // would round P14 + P10 v2 once instead of twice)
+            const unsigned long long m2 = mul2(pk(P10, P10), v2), m3 = mul2(pk(P11, P11), v2);
+            float m2a, m2b, m3a, m3b;
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(ca[0]), "=f"(cb[0]) : "l"(c0));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(ca[1]), "=f"(cb[1]) : "l"(c1));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(m2a), "=f"(m2b) : "l"(m2));
+            asm("mov.b64 {%0, %1}, %2;" : "=f"(m3a), "=f"(m3b) : "l"(m3));
+            ca[2] = __fadd_rn(P14, m2a); cb[2] = __fadd_rn(P14, m2b);
+            ca[3] = __fadd_rn(P15, m3a); cb[3] = __fadd_rn(P15, m3b);
+        };
         // viewport + snap (vf_to_screen) given 1/w
         auto snap = [&](const float c[4], float invw, int32_t& X, int32_t& Y, float& Z) {
             const float xn = __fmul_rn(c[0], invw), yn = __fmul_rn(c[1], invw);
@@ -490,8 +526,12 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         // MUFU.RCP + one Newton step.  Returns false (nothing consumed) when that does not hold.
         auto row_pair = [&]() -> bool {
             float ca[4], cb[4];
+#ifdef VF_GM_NO_F32X2
             clip_pos(r, load_h(r), ca);
             clip_pos(r + 1u, load_h(r + 1u), cb);
+#else
+            clip_pos2(r, ca, cb);
+#endif
             const float ga = __fmul_rn(VF_GUARD_K, ca[3]), gb = __fmul_rn(VF_GUARD_K, cb[3]);
             const bool oka = (ca[3] >= 0x1p-100f) & (ca[3] <= 0x1p100f) & (ca[2] >= 0.0f) & (ca[2] <= ca[3]) &
                              (fabsf(ca[0]) <= ga) & (fabsf(ca[1]) <= ga);
@@ -505,8 +545,22 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             rb = fmaf(rb, -fmaf(cb[3], rb, -1.0f), rb);
             int32_t XA, YA, XB, YB;
             float ZA, ZB;
+#ifdef VF_GM_NO_F32X2
             snap(ca, ra, XA, YA, ZA);
             snap(cb, rb, XB, YB, ZB);
+#else
+            {   // snap of both rows, packed: fma(-yn, hh, hh) == fma(yn, -hh, hh)
+                const unsigned long long r2 = pk(ra, rb);
+                const unsigned long long x2 = fma2(mul2(pk(ca[0], cb[0]), r2), pk(hw, hw), pk(hw, hw));
+                const unsigned long long y2 = fma2(mul2(pk(ca[1], cb[1]), r2), pk(-hh, -hh), pk(hh, hh));
+                float xa, xb, ya, yb;
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(xa), "=f"(xb) : "l"(x2));
+                asm("mov.b64 {%0, %1}, %2;" : "=f"(ya), "=f"(yb) : "l"(y2));
+                XA = __float2int_rn(xa); XB = __float2int_rn(xb);
+                YA = __float2int_rn(ya); YB = __float2int_rn(yb);
+                ZA = DEPTH ? __fmul_rn(ca[2], ra) : 0.0f; ZB = DEPTH ? __fmul_rn(cb[2], rb) : 0.0f;
+            }
+#endif
             const int32_t XAn = __shfl_down_sync(0xffffffffu, XA, 1), YAn = __shfl_down_sync(0xffffffffu, YA, 1);
             const int32_t XBn = __shfl_down_sync(0xffffffffu, XB, 1), YBn = __shfl_down_sync(0xffffffffu, YB, 1);
             float ZAn = 0.0f, ZBn = 0.0f;

@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(VF_GM_WARPS * 32, VF_GM_CTAS)
 k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap dem_map,
              const VfAxis* __restrict__ axis, const float* __restrict__ dem,
              unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims, uint32_t big_capacity,
-             uint32_t* __restrict__ counters, const uint2* __restrict__ segtab, uint32_t nsegs,
+             uint32_t* __restrict__ counters, const uint2* __restrict__ segtab, uint32_t nsegs, uint32_t nfull, uint32_t rows_full,
              unsigned long long* __restrict__ dbg) {
     extern __shared__ __align__(128) unsigned char vf_gm_smem[];
 #ifndef VF_GM_PROFILE                                       // the timing dump costs registers: only in -DVF_GM_PROFILE builds
@@ -303,8 +303,12 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     auto decode = [&](uint32_t task, uint32_t& strip, uint32_t& j0, uint32_t& nr) {
         const uint32_t seg = task / nstrips;
         strip = task - seg * nstrips;
-        const uint2 e = __ldg(segtab + seg);
-        j0 = e.x; nr = e.y;
+        if (seg < nfull) {                                  // the leading segments all have the full height: no table
+            j0 = seg * rows_full; nr = rows_full;           // look-up (an L2 round trip at the start of every task)
+        } else {
+            const uint2 e = __ldg(segtab + seg);
+            j0 = e.x; nr = e.y;
+        }
     };
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t qv_base = vf_smem_u32(&w.qv[0][0]), qcell_base = vf_smem_u32(&w.qcell[0]);

@@ -46,7 +46,7 @@ struct vf_scene {
     uint32_t* d_tile_off = nullptr;      // [n_tiles + 1] offsets | [2] high-water marks (pairs, queued prims)
     uint32_t* d_maxpairs = nullptr;      // = d_tile_off + n_tiles + 1
     uint2* d_segtab = nullptr;           // k_geom_march row segments (first row, rows), rebuilt when G changes
-    uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0;
+    uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0, segtab_nfull = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
@@ -416,6 +416,8 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         VF_CUDA(cudaStreamSynchronize(s->stream));      // frames in flight may still read the old table
         VF_CUDA(cudaMemcpy(s->d_segtab, tab.data(), tab.size() * sizeof(uint2), cudaMemcpyHostToDevice));
         s->segtab_n = (uint32_t)tab.size(); s->segtab_G = s->G; s->segtab_workers = workers; s->segtab_rows = rows;
+        s->segtab_nfull = 0;                             // leading segments (k * rows, rows): decoded without the table
+        while (s->segtab_nfull < tab.size() && tab[s->segtab_nfull].x == s->segtab_nfull * rows && tab[s->segtab_nfull].y == rows) ++s->segtab_nfull;
     }
     const uint32_t nsegs = s->segtab_n, ntasks = nstrips * nsegs;
     // the task dispenser counts in float (vf_geom_march.cuh): exact while every request stays below 2^24
@@ -436,7 +438,7 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         VF_CUDA(cudaMemsetAsync(d_dbg, 0, need * 8, s->stream));
     }
 #define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
-        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, dbg_path ? d_dbg : nullptr)
+        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, s->segtab_nfull, s->segtab_rows, dbg_path ? d_dbg : nullptr)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
     else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }

@@ -583,7 +583,10 @@ k_binsort(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, co
 //             atomicMin((depth<<32)|prim) (depth Less);
 //   shading : thread = pixel; rebuilds the winning primitive, perspective-correct varyings,
 //             fragment stage, exact sRGB8; 4 pixels are packed per 16-byte store.
-__global__ void __launch_bounds__(256, 5)
+#ifndef VF_RASTER_CTAS
+#define VF_RASTER_CTAS 5      // resident CTAs per SM the register budget is set for (4: 0.035 ms, 5: 0.033 ms at c3)
+#endif
+__global__ void __launch_bounds__(256, VF_RASTER_CTAS)
 k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
          const float* __restrict__ dem, const float4* __restrict__ lut,
          const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,

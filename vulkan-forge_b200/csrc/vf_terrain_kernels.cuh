@@ -49,7 +49,9 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_GEOM_THREADS 256
 #define VF_GEOM_VX (VF_GEOM_TX + 1)
 #define VF_GEOM_VY (VF_GEOM_TY + 1)
+#ifndef VF_MICRO_MAX
 #define VF_MICRO_MAX 4         // pixel-centre count up to which one thread rasterises a triangle
+#endif
 #define VF_SERIAL_LINES 256    // one thread walks the runs of a triangle with at most this many lines of its
 #define VF_SERIAL_AREA 4096    // shorter bbox axis and at most this many pixels of area; larger -> binned
 

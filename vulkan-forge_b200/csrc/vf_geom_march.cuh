@@ -3,23 +3,24 @@
 // clip / cull / coverage state of src/terrain/pipeline.rs:107-140 for the implicit grid of
 // src/terrain/mod.rs:553-598).
 //
-//   task     : 32 vertex columns x up to 25 vertex rows of the grid (31 x 24 cells); tasks are handed
-//              out in order by one atomic counter, every warp is its own worker.  The row segments
-//              get shorter towards the end of the grid (host-built table), which keeps the finish
-//              times of the 2368 workers close together (VF_GM_DBG + tools/gm_tasks.py show them)
-//   staging  : the task's 25 x 32 DEM texels are one 2-D TMA box (cp.async.bulk.tensor, 36 texels
-//              wide: a box must start on a 16-byte boundary in global memory, strips start every
-//              31 columns) into the warp's private two-stage ring; the box of task n+1 is in
-//              flight while task n runs
-//   march    : lane = vertex column.  The warp walks down the rows; a lane keeps the previous row's
-//              snapped vertex in registers and gets the right-hand neighbour by shuffle, so a cell
-//              costs one vertex stage + two shuffles + one bbox test.  Cells whose bbox holds no
-//              pixel centre (97 % at G = 4096, 1080p) die here.
-//   queues   : surviving cells are compacted (ballot + popc) into the warp's shared-memory ring and
-//              drained 16 cells = 32 triangles at a time (always full warps): micro triangles are
-//              rasterised by their lane into the L2-resident visibility buffer, longer ones are
-//              compacted again into a second ring and drained 32 at a time by the run rasteriser,
-//              large / clipped ones go to the global queue of k_bin.
+//   task     : 32 vertex columns x up to 31 vertex rows of the grid (31 x 30 cells; 27 rows with depth).  Worker k
+//              starts on tasks k and k + workers, the rest are handed out in order by one (float) atomic counter;
+//              the row segments get shorter towards the end of the grid (host-built table), which keeps the
+//              finish times of the 2368 workers close together (VF_GM_DBG + tools/gm_tasks.py show them)
+//   ahead    : id, place in the grid, texels and axis entries of a task are requested during the task before it
+//   staging  : the task's DEM texels are one 2-D TMA box (cp.async.bulk.tensor, 36 texels wide: a box must start
+//              on a 16-byte boundary in global memory, strips start every 31 columns) into the warp's private
+//              two-stage ring
+//   march    : lane = vertex column.  The warp walks down the rows, two at a time in packed f32x2 arithmetic; a
+//              lane keeps the previous row's snapped vertex in registers and gets the right-hand neighbour by
+//              shuffle, so a cell costs one vertex stage + two shuffles + one bbox test.  Cells whose bbox holds
+//              no pixel centre (92.5 % at G = 4096, 1080p) die here.
+//   queues   : surviving cells are compacted (ballot + popc, predicated stores) into the warp's shared-memory
+//              ring and drained 16 cells = 32 triangles at a time (always full warps, straight-line code):
+//              micro triangles are covered in 32-bit arithmetic by their lane with predicated reductions into
+//              the L2-resident visibility buffer, longer ones are compacted again into a second ring and
+//              drained 32 at a time by the 32-bit run rasteriser, large / clipped ones go to the global queue
+//              of k_binsort.
 // Results do not depend on scheduling: the visibility resolve is order-free (vf_vis_update).
 #pragma once
 #include <type_traits>

@@ -291,7 +291,9 @@ public:
         if (arr.ndim() != 2 || !arr.dtype().is(py::dtype::of<float>()))
             throw py::type_error("argument 'height_r32f': expected a 2-D numpy array of dtype float32");
         if (!(arr.flags() & py::array::c_style)) throw std::runtime_error("height must be C-contiguous float32[H,W]");
-        held_height_ = arr;                                   // the copy is in flight after this call returns
+        // The DMA is in flight after this call returns: the array stays referenced until the batch that
+        // renders from it has been collected (or the scene is destroyed, which synchronises first).
+        pending_heights_.push_back(arr);
         check(vf_scene_set_height_f32_async(scene_, static_cast<const float*>(arr.data()), (uint32_t)arr.shape(1), (uint32_t)arr.shape(0)));
     }
     int render_batch_rgba_async(py::object cameras) {
@@ -302,6 +304,8 @@ public:
         int ticket = -1;
         check(vf_scene_render_batch_async(scene_, blocks.data(), n, out.mutable_data(), &ticket));
         in_flight_[ticket] = out;
+        ticket_heights_[ticket] = std::move(pending_heights_);   // uploads this batch (or an earlier one) consumes
+        pending_heights_.clear();
         return ticket;
     }
     py::array_t<uint8_t> collect(int ticket) {
@@ -313,6 +317,7 @@ public:
         }
         py::array_t<uint8_t> out = it->second;
         in_flight_.erase(it);
+        ticket_heights_.erase(ticket);                        // the batch is done, so are the uploads queued before it
         return out;
     }
     // frames stay on the device; returns elapsed milliseconds (host clock around a synchronous call)
@@ -355,7 +360,8 @@ private:
     uint32_t width_, height_, grid_ = 128;
     bool spike_, lut_unorm_ = false;
     vf_scene* scene_ = nullptr;
-    py::object held_height_;
+    std::vector<py::object> pending_heights_;
+    std::map<int, std::vector<py::object>> ticket_heights_;
     std::map<int, py::array_t<uint8_t>> in_flight_;
     Globals globals_;
     M4 view_, proj_;

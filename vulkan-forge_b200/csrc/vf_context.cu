@@ -23,8 +23,9 @@ int vf_set_error(int code, const char* fmt, ...) {
 extern "C" const char* vf_last_error(void) { return g_err; }
 
 static std::mutex g_mu;
-static int g_device = -1;                 // device the tables live on
-static float* g_thr_dev = nullptr;
+static int g_device = -1;                 // device selected by the last vf_init
+static const int kMaxDevices = 64;
+static float* g_thr_dev[kMaxDevices] = {nullptr};   // the sRGB threshold table, one copy per device that has been used
 static float g_thr_host[256];
 static bool g_thr_built = false;
 
@@ -93,23 +94,23 @@ extern "C" int vf_init(int device) {
         }
     }
     if (device >= n) return vf_set_error(VF_E_INVALID, "device %d out of range (%d devices)", device, n);
+    if (device >= kMaxDevices) return vf_set_error(VF_E_INVALID, "device %d: at most %d devices are supported", device, kMaxDevices);
     VF_CUDA(cudaSetDevice(device));
-    if (g_device != device || !g_thr_dev) {
+    if (!g_thr_dev[device]) {                 // scenes of another device keep using their own copy
         build_thresholds();
-        if (g_thr_dev && g_device >= 0 && g_device != device) { /* keep old table: other scenes may use it */ }
         float* p = nullptr;
         VF_CUDA(cudaMalloc(&p, sizeof g_thr_host));
         VF_CUDA(cudaMemcpy(p, g_thr_host, sizeof g_thr_host, cudaMemcpyHostToDevice));
-        g_thr_dev = p;
-        g_device = device;
+        g_thr_dev[device] = p;
     }
+    g_device = device;
     return VF_OK;
 }
 
 int vf_require_device() {
     {
         std::lock_guard<std::mutex> lk(g_mu);
-        if (g_device >= 0 && g_thr_dev) {
+        if (g_device >= 0 && g_thr_dev[g_device]) {
             cudaError_t e = cudaSetDevice(g_device);
             if (e == cudaSuccess) return VF_OK;
         }
@@ -117,7 +118,13 @@ int vf_require_device() {
     return vf_init(-1);
 }
 
-const float* vf_srgb_thresholds_dev() { return g_thr_dev; }
+// table of the CURRENT device (nullptr if vf_init never ran for it)
+const float* vf_srgb_thresholds_dev() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return nullptr;
+    return g_thr_dev[dev];
+}
+int vf_current_device() { return g_device; }
 
 extern "C" int vf_device_info(int device, vf_device_info_t* out) {
     int n = 0;

@@ -330,6 +330,9 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     auto got_task = [&](uint32_t t) -> uint32_t { return 2u * nworkers + (uint32_t)__uint_as_float(__shfl_sync(0xffffffffu, t, 0)); };
     auto issue = [&](bool valid, uint32_t strip, uint32_t j0, uint32_t stage) {   // lane 0: start the TMA of a task into `stage`
         if (TMA && lane == 0 && valid) {
+            // The stage was read (generic proxy) by the task before the current one; the __syncwarp() that closes
+            // every task orders those reads before this point, the proxy fence orders them before the bulk write.
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             vf_mbar_expect_tx(&w.mbar[stage], VROWS * VF_GM_BOX_X * 4u);
             vf_tma_load_2d(&w.dem[stage][0], &dem_map, (int)((strip * VF_GM_QCOLS) & ~3u), (int)j0, &w.mbar[stage]);
         }

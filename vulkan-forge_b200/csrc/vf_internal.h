@@ -10,6 +10,7 @@
 int vf_set_error(int code, const char* fmt, ...);
 int vf_require_device();                 // VF_OK or VF_E_NO_DEVICE (lazy vf_init(-1))
 const float* vf_srgb_thresholds_dev();   // 256 floats on the current device (thr[0] = 0)
+int vf_current_device();                 // device of the last vf_init (-1: none yet)
 const float* vf_srgb_thresholds_host();
 const uint8_t* vf_palette_bytes(int lut_id);   // 1024 bytes or nullptr
 

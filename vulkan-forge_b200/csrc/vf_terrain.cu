@@ -26,7 +26,13 @@ static vf_tmap_encode_fn tmap_encoder() {
     return fn;
 }
 
+// launch configuration that depends on the device (SM count, opt-in shared memory, cooperative grid size):
+// cached per device ordinal, not per process -- vf_init(device) may switch devices within one process
+struct VfDevCache { int sm_count = 0; bool gm_attr = false; int binsort_ctas = 0; };
+static VfDevCache g_dev_cache[64];
+
 struct vf_scene {
+    int device = 0;                      // CUDA device the scene's buffers, streams and events live on
     int W = 0, H = 0;
     uint32_t G = 0;
     int lut_id = 0, lut_unorm = 0;
@@ -53,6 +59,7 @@ struct vf_scene {
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
     alignas(64) CUtensorMap dem_map_gm[2];  // same tensor, one box per warp task of k_geom_march: [0] 36x31 floats, [1] 36x27 (depth)
     bool use_tma = false;                // grid == DEM with identity texel mapping
+    bool geom_tiled = false;             // VF_GEOM_TILED at creation: tiled k_geom instead of k_geom_march (A/B runs)
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
     // front image render; swapped in by the next submit
     float* d_dem_back = nullptr;
@@ -182,9 +189,17 @@ static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pit
 
 static void scene_resolve_readers(vf_scene* s, const float* image);
 
+// every entry point works on the scene's own device, whatever vf_init selected since its creation
+static int scene_bind(const vf_scene* s) {
+    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    VF_CUDA(cudaSetDevice(s->device));
+    return VF_OK;
+}
+
 static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "height image cannot be empty");
     const uint32_t pitch = (w + 3u) & ~3u;            // rows start 16-byte aligned (TMA-ready)
+    if (int rcb = scene_bind(s)) return rcb;
     scene_resolve_readers(s, nullptr);                // batches in flight read the images replaced below
     if (s->upload_stream) VF_CUDA(cudaStreamSynchronize(s->upload_stream));
     s->back_pending = false;
@@ -239,6 +254,8 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     s->tiles_y = (uint32_t)(h + VF_TILE - 1) / VF_TILE;
     s->n_tiles = s->tiles_x * s->tiles_y;
     s->n_slots = VF_MAX_SLOTS;
+    s->geom_tiled = getenv("VF_GEOM_TILED") != nullptr;
+    if (cudaGetDevice(&s->device) != cudaSuccess) s->device = 0;
 #define SC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { scene_free(s); \
         return vf_set_error(e_ == cudaErrorMemoryAllocation ? VF_E_OOM : VF_E_CUDA, \
         "%s failed: %s", #call, cudaGetErrorString(e_)); } } while (0)
@@ -283,6 +300,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
 
 extern "C" void vf_scene_destroy(vf_scene* s) {
     if (!s) return;
+    cudaSetDevice(s->device);
     cudaStreamSynchronize(s->stream);
     if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);       // batches / uploads still in flight
     if (s->upload_stream) cudaStreamSynchronize(s->upload_stream);
@@ -329,7 +347,7 @@ extern "C" int vf_scene_last_stats(const vf_scene* s, vf_frame_stats_t* out) {
 }
 
 extern "C" int vf_scene_set_stream(vf_scene* s, void* cuda_stream) {
-    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
+    if (int rcb = scene_bind(s)) return rcb;
     VF_CUDA(cudaStreamSynchronize(s->stream));
     if (s->own_stream) { cudaStreamDestroy(s->stream); s->own_stream = false; }
     if (cuda_stream) s->stream = (cudaStream_t)cuda_stream;
@@ -374,19 +392,17 @@ static uint32_t clear_rgba8() {
 // k_geom_march: persistent grid of warp workers; rows per task shrink on coarse grids so that every
 // warp of the machine gets a few tasks
 static int launch_geom_march(vf_scene* s, const VfFrame& f) {
-    static int sm_count = 0;
-    static bool attr_done = false;
+    VfDevCache& dc = g_dev_cache[s->device & 63];
     const size_t smem_d = VF_GM_WARPS * sizeof(VfGmWarpT<true>), smem_n = VF_GM_WARPS * sizeof(VfGmWarpT<false>);
-    if (!attr_done) {
-        int dev = 0;
-        VF_CUDA(cudaGetDevice(&dev));
-        VF_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    if (!dc.gm_attr) {                   // cudaFuncSetAttribute applies to the current device only
+        VF_CUDA(cudaDeviceGetAttribute(&dc.sm_count, cudaDevAttrMultiProcessorCount, s->device));
 #define VF_GM_ATTR(T, D, S) VF_CUDA(cudaFuncSetAttribute(k_geom_march<T, D, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((D) ? smem_d : smem_n)))
         VF_GM_ATTR(true, true, true);   VF_GM_ATTR(true, true, false);   VF_GM_ATTR(true, false, true);   VF_GM_ATTR(true, false, false);
         VF_GM_ATTR(false, true, true);  VF_GM_ATTR(false, true, false);  VF_GM_ATTR(false, false, true);  VF_GM_ATTR(false, false, false);
 #undef VF_GM_ATTR
-        attr_done = true;
+        dc.gm_attr = true;
     }
+    const int sm_count = dc.sm_count;
     const uint32_t gm = s->G - 1;
     const uint32_t nstrips = (gm + VF_GM_QCOLS - 1) / VF_GM_QCOLS;
     const uint32_t per_sm = VF_GM_CTAS;     // CTAs per SM (launch bounds of k_geom_march)
@@ -464,6 +480,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     build_frame(s, u44, &f);
     static const uint32_t clear = clear_rgba8();
     const float* thr = vf_srgb_thresholds_dev();
+    if (!thr) return vf_set_error(VF_E_CUDA, "no sRGB table on device %d (vf_init has not run for it)", s->device);
     uint8_t* frame = s->d_frame + (size_t)slot * s->W * s->H * 4;
     VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[0], s->stream));
@@ -471,7 +488,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaMemsetAsync(s->d_visbuf, f.depth ? 0xff : 0x00, (size_t)s->W * s->H * 8, s->stream));
         s->visbuf_depth = f.depth;
     }
-    if (!f.sparse || getenv("VF_GEOM_TILED")) {   // general matrices; also kept for A/B runs
+    if (!f.sparse || s->geom_tiled) {   // general matrices; also kept for A/B runs
         const uint32_t gb = (s->G - 1 + VF_GEOM_TX - 1) / VF_GEOM_TX;
         if (s->use_tma)
             k_geom<true><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
@@ -489,11 +506,10 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         s->submit_skipped_bins = true;
     } else {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
         if (s->bin_hold) --s->bin_hold;
-        static int binsort_ctas = 0;
+        int& binsort_ctas = g_dev_cache[s->device & 63].binsort_ctas;
         if (!binsort_ctas) {
-            int dev = 0, sms = 0, per_sm = 0;
-            VF_CUDA(cudaGetDevice(&dev));
-            VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            int sms = 0, per_sm = 0;
+            VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
             VF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_binsort, 256, 0));
             binsort_ctas = sms * std::min(std::max(per_sm, 1), 2);
         }
@@ -551,7 +567,9 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
     s->submit_skipped_bins = false;
     for (int k = 0; k < n; ++k) {
         const int slot = k % VF_MAX_SLOTS;
-        if (out_host && s->slot_used[slot]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
+        // a frame slot may still be draining to the host on copy_stream (an earlier batch, possibly one
+        // submitted with vf_scene_render_batch_async): wait for that copy whatever this call does with its frames
+        if (s->slot_used[slot]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
         rc = scene_enqueue(s, u44xn + (size_t)k * 44, slot, d_vis);
         if (rc) return rc;
         if (out_host) {
@@ -599,7 +617,7 @@ static int scene_check_overflow(vf_scene* s, int hslot, bool skipped_bins) {
 // (an overflowed frame leaves a clean visibility buffer: k_raster always runs to completion).
 static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, bool apply_pending = true) {
     if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
-    int rc = vf_require_device();
+    int rc = scene_bind(s);
     if (rc) return rc;
     for (int attempt = 0; attempt < 8; ++attempt) {
         rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending);
@@ -658,6 +676,7 @@ static void scene_resolve_readers(vf_scene* s, const float* image) {
 
 extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (!s || !host) return vf_set_error(VF_E_INVALID, "null argument");
+    if (int rcb = scene_bind(s)) return rcb;
     const uint32_t pitch = (w + 3u) & ~3u;
     if (w != s->Wd || h != s->Hd || pitch != s->pitch || !s->d_dem) return scene_upload_dem(s, host, w, h);   // new size: synchronous path
     if (!s->upload_stream) {
@@ -686,7 +705,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
 
 extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int n, uint8_t* out_rgba_host, int* ticket) {
     if (!s || !u44xn || n <= 0 || !out_rgba_host || !ticket) return vf_set_error(VF_E_INVALID, "invalid argument");
-    int rc = vf_require_device();
+    int rc = scene_bind(s);
     if (rc) return rc;
     int id = -1;
     for (int k = 0; k < 4; ++k) if (!s->tickets[k].busy) { id = k; break; }
@@ -711,6 +730,7 @@ extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int 
 
 extern "C" int vf_scene_wait(vf_scene* s, int ticket) {
     if (!s || ticket < 0 || ticket >= 4 || !s->tickets[ticket].busy) return vf_set_error(VF_E_INVALID, "invalid ticket");
+    if (int rcb = scene_bind(s)) return rcb;
     const int rc = ticket_resolve(s, ticket);
     s->tickets[ticket].busy = false;
     return rc;
@@ -745,9 +765,10 @@ int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t p
                          float* lo, float* hi, cudaStream_t stream);
 
 extern "C" int vf_scene_auto_height_range(vf_scene* s, float* h_min, float* h_max) {
-    if (!s) return vf_set_error(VF_E_INVALID, "null scene");
     float lo, hi;
-    int rc = scene_apply_pending_dem(s);
+    int rc = scene_bind(s);
+    if (rc) return rc;
+    rc = scene_apply_pending_dem(s);
     if (rc) return rc;
     rc = vf_dem_minmax_device(s->d_dem, s->Wd, s->Hd, s->pitch, 1, &lo, &hi, s->stream);
     if (rc) return rc;

@@ -25,7 +25,18 @@ import sys
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-sys.path.insert(0, os.path.join(ROOT, "vulkan-forge_b200", "python"))
+PKG = os.path.join(ROOT, "vulkan-forge_b200", "python")
+
+
+def _load_by_path(name, rel):
+    """Pure-Python helper modules of the package (synthetic DEM, orbit cameras) loaded by file path, WITHOUT importing
+    the package: the reference arm must not load the product's native libraries."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(name, os.path.join(PKG, "vulkan_forge", rel))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
 
 W, H, G, DEM_N, DEM_SEED, CMAP = 1920, 1080, 4096, 4096, 0, "terrain"
 WORKLOAD = "c3: Scene 1920x1080, DEM 4096^2 seed 0, grid 4096, terrain LUT, NORTHSTAR (sun 35/120, exposure 1.1, auto 1-99%)"
@@ -101,6 +112,12 @@ def host_threads():
         return os.cpu_count() or 1
 
 
+def workload_config(frames):
+    """The same object in both arms (the driver compares them)."""
+    return {"workload": WORKLOAD, "frames_per_step_per_gpu": frames, "l2": "flushed between steps (256 MiB write)",
+            "sharding": "independent frames per GPU, no collective"}
+
+
 def cpu_reference_fps(frames_budget_s, dem, uniforms, hmin, hmax, min_frames=2, max_frames=64):
     """Reference CPU path stand-in (oracle, all host threads) on a bounded sample of the workload."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -118,25 +135,26 @@ def cpu_reference_fps(frames_budget_s, dem, uniforms, hmin, hmax, min_frames=2, 
 
 
 def run_reference(args):
-    """--impl reference: CPU only; rank 0 alone works."""
+    """--impl reference: CPU only; rank 0 alone works.  Nothing of the product is imported here: cameras and the DEM
+    come from the package's pure-Python helpers loaded by path, uniforms and frames from oracle/."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     import numpy as np
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import vf_oracle as oracle
-    from vulkan_forge._synthetic import synthetic_dem
-    import vulkan_forge as vf
+    synthetic_dem = _load_by_path("vf_synthetic", "_synthetic.py").synthetic_dem
+    orbit_cameras = _load_by_path("vf_orbit", "orbit.py").orbit_cameras
     dem = synthetic_dem(DEM_SEED, DEM_N)
     hmin, hmax = (float(x) for x in oracle.h_range(dem))
-    cams = vf.orbit_cameras(max(args.frames, 1) * 4)
+    cams = orbit_cameras(max(args.frames, 1) * 4)
     us = [oracle.look_at_uniforms(W, H, c[0], c[1], c[2], c[3], c[4], c[5], sun=oracle.sun_dir(35.0, 120.0), exposure=1.1,
                                   h_min=hmin, h_max=hmax, normalize_sun=False) for c in cams]
     lut = np.fromfile(os.path.join(ROOT, "tests", "golden", f"lut_{CMAP}.rgba"), np.uint8)
-    per_step = args.ref_frames
+    per_step = args.ref_frames                        # bounded sample: the first `per_step` frames of every step
 
     def step(k):
         for j in range(per_step):
-            oracle.render_terrain(W, H, G, dem, us[(k * per_step + j) % len(us)], lut, mode=oracle.MODE_NORTHSTAR,
+            oracle.render_terrain(W, H, G, dem, us[(k * args.frames + j) % len(us)], lut, mode=oracle.MODE_NORTHSTAR,
                                   h_min=hmin, h_max=hmax, threads=host_threads())
     for k in range(args.warmup):
         step(k)
@@ -147,12 +165,13 @@ def run_reference(args):
     fps = args.steps * per_step / dt
     line = {
         "impl": "reference", "metric": "terrain frames/s (1080p, 4096^2 DEM)", "value": fps, "unit": "frames/s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": args.frames / fps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": per_step, "l2": "n/a (CPU)", "sharding": "rank 0 only"},
+        "config": workload_config(args.frames),
         "mpix_per_s": fps * W * H / 1e6,
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": host_threads(), "kind": "port",
-                         "sample": f"{args.steps}x{per_step} frames of the same workload; oracle/ (C + OpenMP); the reference's wgpu software path is unavailable on this box"},
+                         "sample": f"{per_step} of the {args.frames} frames of each of {args.steps} steps ({dt:.1f} s); oracle/ (C + OpenMP, all host threads); "
+                                   "ms_per_step is the sample's rate scaled to a whole step; the reference's wgpu software path is unavailable on this box"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -172,6 +191,7 @@ def main():
     if args.impl == "reference":
         return run_reference(args)
 
+    sys.path.insert(0, PKG)
     import numpy as np
     import torch
     import vulkan_forge as vf
@@ -257,6 +277,24 @@ def main():
     e2e_s = time.perf_counter() - t0
     barrier()
 
+    # ---- parity gate of this very run (outside the timed regions, rank 0): frame 0 of the timed batch against the oracle ----
+    parity = None
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import vf_oracle as oracle
+        lut = np.fromfile(os.path.join(ROOT, "tests", "golden", f"lut_{CMAP}.rgba"), np.uint8)
+        u0 = np.asarray(blocks[0])
+        got = np.asarray(sc.render_batch_rgba(blocks[0:1])[0])
+        sc.set_uniforms_raw(u0)
+        gvis = sc.debug_visibility()
+        ref, rvis = oracle.render_terrain(W, H, G, dem, u0, lut, mode=oracle.MODE_NORTHSTAR, depth=False, h_min=float(hmin),
+                                          h_max=float(hmax), threads=host_threads(), want_prim=True)
+        d = np.abs(got.astype(np.int16) - ref.astype(np.int16)).max(-1)
+        olo, ohi = oracle.h_range(dem)
+        parity = {"frames_checked": 1, "frame": "frame 0 of the timed batch", "within_1lsb": float((d <= 1).mean()), "bit_identical": bool((d == 0).all()),
+                  "coverage_mismatch": int((gvis != rvis).sum()), "percentile_range_bit_exact": bool(np.float32(hmin) == olo and np.float32(hmax) == ohi),
+                  "against": "oracle/ (CPU restatement; pixel parity with the reference's wgpu renderer is unpinned: it cannot run on this box)"}
+
     t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -277,7 +315,7 @@ def main():
         issue, winst = None, ncu_traffic({"ms_geom": "k_geom", "ms_raster": "k_raster"}.get(dom, "") + "_warp_inst")
         if winst and clocks and clocks.get("sm_mhz"):
             slots = 148 * 4 * clocks["sm_mhz"] * 1e6 * kmed[dom] * 1e-3          # one warp instruction per SM sub-partition per clock
-            issue = {"warp_inst_per_launch": winst, "issue_slots": slots, "frac": winst / slots, "source": "profiles/dram_traffic.json"}
+            issue = {"warp_inst_per_launch": winst, "issue_slots": slots, "frac": winst / slots, "source": "warp instructions: committed ncu capture (profiles/dram_traffic.json); time and clock: this run"}
         cpu = None
         if world == 1:                                     # reported at N=1 only
             us = [np.asarray(blocks[i]) for i in range(min(F, 4))]
@@ -288,15 +326,16 @@ def main():
             "metric": "terrain frames/s (1080p, 4096^2 DEM)", "value": fps, "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD,
-                       "frames_per_step_per_gpu": F, "l2": "flushed between steps (256 MiB write)", "sharding": "independent frames per GPU, no collective", "host_binding": numa},
+            "config": workload_config(F), "host_binding": numa,
             "mpix_per_s": fps * W * H / 1e6,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},
             "gpu_launches": args.steps * F * 2,   # k_geom_march + k_raster per frame (value leg); k_binsort is not launched while frames queue nothing for it
-            "roofline": {"bound": "hbm", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_raster"}[dom],
+            "parity": parity,
+            "roofline": {"bound": "hbm", "limited_by": "instruction issue (see issue)", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_raster"}[dom],
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic({"ms_geom": "k_geom", "ms_bin": "k_bin", "ms_raster": "k_raster"}[dom]),
+                         "traffic_source": "committed ncu --set full capture (profiles/dram_traffic.json), not measured in this run",
                          "peak_source": peak_kind, "algorithmic_bytes_per_launch": dom_bytes, "kernel_ms": kmed[dom],
                          "frame": {"algorithmic_bytes": ALGO_BYTES_FRAME, "ms": kmed["ms_total"], "achieved": frame_achieved, "frac": frame_achieved / peak},
                          "kernels_ms": kmed, "issue": issue},

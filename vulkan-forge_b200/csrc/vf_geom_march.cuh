@@ -55,7 +55,7 @@ struct VfGmWarpT {
     alignas(8) uint64_t mbar[2];
     float wz[VfGmDim<DEPTH>::VROWS], kz[VfGmDim<DEPTH>::VROWS];   // per row: z*spacing, 0.25*cos(1.1 z)
     int ty[VfGmDim<DEPTH>::VROWS];                       // per row: texel row
-    alignas(8) int2 qv[4][VF_GM_QCAP];                   // queued cells: snapped (X, Y) of a, b, c, d
+    alignas(16) int4 qv[2][VF_GM_QCAP];                  // queued cells: raw snapped (x, y) of (a, b) and of (c, d), see vf_gm_raw
     float qz[DEPTH ? 4 : 1][DEPTH ? VF_GM_QCAP : 1];     // depth only
     uint32_t qcell[VF_GM_QCAP];                          // cell index | bit 31: rebuild from scratch (clip flags mixed)
     alignas(8) int2 nv[3][VF_GM_NCAP];                   // queued long triangles: snapped (X, Y) of the vertices
@@ -70,6 +70,43 @@ struct VfGmQueues {
     __device__ __forceinline__ uint32_t pack() const { return qhead | (qn << 8) | (nhead << 16) | (nn << 24); }
     __device__ __forceinline__ void unpack(uint32_t v) { qhead = v & 255u; qn = (v >> 8) & 255u; nhead = (v >> 16) & 255u; nn = v >> 24; }
 };
+
+// Snap without a float -> int conversion, and the cell cull without a bounding box.
+//   raw     : for a vertex inside the fast guard band (|X|, |Y| <= 2^22 - 256 sub-pixels) the march keeps
+//             raw = float_as_int(-xa + VF_GM_MAGIC), xa = fma(xn, 256 hw, 256 hw) the screen position in sub-pixels.
+//             The sum lies in [2^23, 2^24) where floats are the integers, so the FADD rounds -xa to nearest-even
+//             exactly as cvt.rni does (the constant is even), and raw = bits(MAGIC) + (-X - 128): X = VF_GM_RAWC - raw.
+//   key     : bits 8..23 of raw are floor((-X - 128) / 256) + 2^14, the index of the last pixel centre
+//             (sub-pixel 128 mod 256) at or below -X.  Two vertices with the same index have no centre c with
+//             mn <= c < mx between them.  A centre ON the right / bottom extreme of a front-facing triangle is
+//             never covered (its two edges there run up, resp. the bottom edge runs right: not top-left), so a
+//             cell whose four vertices share the x index or share the y index draws nothing.  One PRMT packs the
+//             two indices of a vertex; (Ka^Kb)|(Ka^Kc)|(Ka^Kd) has a zero half exactly when one axis is shared.
+#define VF_GM_MAGIC 12582784.0f                       // 1.5 * 2^23 - 128
+#define VF_GM_RAWC  0x4B3FFF80                        // bits(VF_GM_MAGIC) - 128 : X = VF_GM_RAWC - raw
+#define VF_GM_FAST_PX 16383.0f                        // fast guard band: |X| <= 16383 px keeps the sum inside the binade
+__device__ __forceinline__ uint32_t vf_gm_key(int32_t rx, int32_t ry) {
+    uint32_t k;
+    asm("prmt.b32 %0, %1, %2, 0x6521;" : "=r"(k) : "r"(rx), "r"(ry));     // bytes 1,2 of rx | bytes 1,2 of ry
+    return k;
+}
+// (Ka^Kb)|(Ka^Kc)|(Ka^Kd)
+__device__ __forceinline__ uint32_t vf_gm_keydiff(uint32_t ka, uint32_t kb, uint32_t kc, uint32_t kd) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0x7e;" : "=r"(d) : "r"(ka), "r"(kb), "r"(kc));          // (a^b)|(a^c) == not all three equal
+    asm("lop3.b32 %0, %1, %2, %3, 0xf6;" : "=r"(d) : "r"(d), "r"(ka), "r"(kd));           // d | (a^d)
+    return d;
+}
+// both halves of the key difference non-zero (and the lane owns a cell): LOP3 with a predicate result + one ISETP
+__device__ __forceinline__ bool vf_gm_cell_live(uint32_t d, bool cellv) {
+    uint32_t r;
+    asm("{\n\t.reg .pred p, q;\n\t.reg .b32 t;\n\t"
+        "setp.ne.u32 q, %2, 0;\n\t"
+        "lop3.and.b32 t|p, %1, 0xffff, 0, 0xC0, q;\n\t"          // p = ((d & 0xffff) != 0) && cellv
+        "setp.gt.u32.and p, %1, 0xffff, p;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(r) : "r"(d), "r"((uint32_t)cellv));
+    return r != 0u;
+}
 
 // Full per-triangle treatment of a cell whose vertices are not all inside the guard band: the
 // vertex stage is redone from the grid (same code as k_bin / k_raster).  0: nothing to draw,
@@ -86,20 +123,20 @@ static __device__ __noinline__ int vf_gm_rebuild(const VfFrame& f, const VfAxis*
     return 1;
 }
 
-// one covered sample -> visibility buffer
-template <bool DEPTH>
-__device__ __forceinline__ void vf_gm_emit(const VfFrame& f, unsigned long long* __restrict__ vis, const VfSubTri& t,
-                                           uint32_t nbias, uint32_t prim, int px, int py, int64_t ed[3]) {
-    float zf = 0.0f;
-    if (DEPTH) {
-        float b[3];
-#pragma unroll
-        for (int i = 0; i < 3; ++i) ed[i] += (int64_t)((nbias >> i) & 1u);     // vf_edges_unbias
-        vf_barycentric(ed, b);
-        zf = vf_depth_at(t, b);
-        if (!(zf < 1.0f)) return;
-    }
-    vf_vis_update(vis + (size_t)py * f.W + px, DEPTH, prim, zf);
+// One covered sample of the depth variant -> visibility buffer.  e0..e2 are the BIASED edge values of the sample
+// (they fit 32 bits: 0 <= E_i < 2^31 on a covered sample of a micro or serial triangle).  vf_barycentric divides
+// by e0 + e1 + e2, which is twice the triangle's area at every sample: rinv = 1 / float(-area2) is taken once per
+// triangle (vf_gm_rinv) and the weights are the same floats as vf_barycentric's.
+__device__ __forceinline__ float vf_gm_rinv(int64_t area2) { return __fdiv_rn(1.0f, (float)(-area2)); }
+__device__ __forceinline__ void vf_gm_emit_depth(unsigned long long* __restrict__ key64, const VfSubTri& t, float rinv, uint32_t nbias,
+                                                 uint32_t prim, uint32_t e0, uint32_t e1, uint32_t e2) {
+    float b[3];
+    b[0] = __fmul_rn((float)(int32_t)(e0 + (nbias & 1u)), rinv);                 // vf_edges_unbias + vf_barycentric
+    b[1] = __fmul_rn((float)(int32_t)(e1 + ((nbias >> 1) & 1u)), rinv);
+    b[2] = __fmul_rn((float)(int32_t)(e2 + ((nbias >> 2) & 1u)), rinv);
+    const float zf = vf_depth_at(t, b);
+    if (!(zf < 1.0f)) return;
+    vf_vis_update(key64, true, prim, zf);
 }
 
 // drain groups of 32 long triangles (whatever is left when `all`)
@@ -118,27 +155,11 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
             vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1);
             VfEdges es;
             vf_edges_setup(t, x0, y0, es);
-#ifdef VF_GM_THIN64                                          // A/B: the 64-bit walk of the tiled k_geom
-            vf_thin_raster(es, x0, x1, y0, y1, [&](int px, int py, int64_t ed[3]) {
-                vf_gm_emit<DEPTH>(f, vis, t, es.nbias, prim, px, py, ed);
-            });
-#else
-            vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](bool covered, uint32_t idx, int m, int c, bool cols) {
+            const float rinv = DEPTH ? vf_gm_rinv(vf_area2(t)) : 0.0f;
+            vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](bool covered, uint32_t idx, uint32_t e0, uint32_t e1, uint32_t e2) {
                 if (!DEPTH) { vf_vis_max_if(covered, vis + idx, prim); return; }
-                if (!covered) return;
-                float zf = 0.0f;
-                if (DEPTH) {
-                    int64_t ed[3];
-                    float b[3];
-                    vf_edges_at(es, cols ? m : c, cols ? c : m, ed);
-                    vf_edges_unbias(es, ed);
-                    vf_barycentric(ed, b);
-                    zf = vf_depth_at(t, b);
-                    if (!(zf < 1.0f)) return;
-                }
-                vf_vis_update(vis + idx, DEPTH, prim, zf);
+                if (covered) vf_gm_emit_depth(vis + idx, t, rinv, es.nbias, prim, e0, e1, e2);
             });
-#endif
         }
         q.nhead = (q.nhead + take) & (VF_GM_NCAP - 1u);
         q.nn -= take;
@@ -172,11 +193,14 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
 #pragma unroll
                 for (int v = 0; v < 3; ++v) { t.v[v].X = tr.v[v].X; t.v[v].Y = tr.v[v].Y; t.v[v].zn = tr.v[v].zn; }
             } else {                                     // T0 = (a, c, b), T1 = (b, c, d): src/terrain/mod.rs:581
+                // ring entry: qv[0] = raw (a.x, a.y, b.x, b.y), qv[1] = raw (c.x, c.y, d.x, d.y); X = VF_GM_RAWC - raw
+                const int2* ab = reinterpret_cast<const int2*>(&w.qv[0][slot]);
+                const int2* cd = reinterpret_cast<const int2*>(&w.qv[1][slot]);
+                const int2 v0 = ab[k], v1 = cd[0], v2 = k ? cd[1] : ab[1];
+                t.v[0].X = VF_GM_RAWC - v0.x; t.v[0].Y = VF_GM_RAWC - v0.y;
+                t.v[1].X = VF_GM_RAWC - v1.x; t.v[1].Y = VF_GM_RAWC - v1.y;
+                t.v[2].X = VF_GM_RAWC - v2.x; t.v[2].Y = VF_GM_RAWC - v2.y;
                 const uint32_t i0 = k, i2 = 1u + 2u * k;
-                const int2 v0 = w.qv[i0][slot], v1 = w.qv[2][slot], v2 = w.qv[i2][slot];
-                t.v[0].X = v0.x; t.v[0].Y = v0.y;
-                t.v[1].X = v1.x; t.v[1].Y = v1.y;
-                t.v[2].X = v2.x; t.v[2].Y = v2.y;
                 if (DEPTH) { t.v[0].zn = w.qz[i0][slot]; t.v[1].zn = w.qz[2][slot]; t.v[2].zn = w.qz[i2][slot]; }
             }
             // Classification and micro coverage in straight-line code: a divergent region costs the warp its
@@ -211,11 +235,11 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
             // the (at most four) samples: the first one without a loop, the others along the row, then down
             int32_t e0 = E[0], e1 = E[1], e2 = E[2];
             uint32_t idx = (uint32_t)y0 * f.W + (uint32_t)x0;                   // sample index in the frame
+            const float rinv = DEPTH ? vf_gm_rinv(area2) : 0.0f;
             if (!DEPTH) {
                 vf_vis_max_if(micro && (e0 | e1 | e2) >= 0, vis + idx, prim);
             } else if (micro && (e0 | e1 | e2) >= 0) {
-                int64_t ed[3] = {e0, e1, e2};
-                vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0, y0, ed);
+                vf_gm_emit_depth(vis + idx, t, rinv, nbias, prim, (uint32_t)e0, (uint32_t)e1, (uint32_t)e2);
             }
             if (micro && npx > 1) {
                 const int32_t a0 = A[0] * VF_SUBPIX, a1 = A[1] * VF_SUBPIX, a2 = A[2] * VF_SUBPIX;
@@ -233,8 +257,7 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                     if (!DEPTH) {
                         vf_vis_max_if(covered, vis + idx, prim);
                     } else if (covered) {
-                        int64_t ed[3] = {e0, e1, e2};
-                        vf_gm_emit<DEPTH>(f, vis, t, nbias, prim, x0 + dx, y0 + dy, ed);
+                        vf_gm_emit_depth(vis + idx, t, rinv, nbias, prim, (uint32_t)e0, (uint32_t)e1, (uint32_t)e2);
                     }
                 }
             }
@@ -313,6 +336,10 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     };
     const uint32_t below = (1u << lane) - 1u;
     const uint32_t qv_base = vf_smem_u32(&w.qv[0][0]), qcell_base = vf_smem_u32(&w.qcell[0]);
+    // fast guard band per axis: the 8x guard band of the clipper, narrowed where 9 x half the frame would exceed
+    // VF_GM_FAST_PX pixels (frames wider than 3640 px) so that the raw snap stays inside its binade
+    float gfx = fminf(VF_GUARD_K, __fmul_rn(__fsub_rn(__fdiv_rn(VF_GM_FAST_PX, f.hw), 1.0f), 0.999f));
+    float gfy = fminf(VF_GUARD_K, __fmul_rn(__fsub_rn(__fdiv_rn(VF_GM_FAST_PX, f.hh), 1.0f), 0.999f));
 
     // the dispenser's answer takes an L2 round trip: it is asked for one task before it is needed
     // The counter is kept as a FLOAT (exact below 2^24 tasks; the host falls back to more rows per task
@@ -378,6 +405,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
     VF_PIN(V4); VF_PIN(V5); VF_PIN(V6); VF_PIN(V8); VF_PIN(V9); VF_PIN(V10);
     VF_PIN(P0); VF_PIN(P5); VF_PIN(P10); VF_PIN(P11); VF_PIN(P14); VF_PIN(P15);
     VF_PIN(exag); VF_PIN(hw); VF_PIN(hh);
+    VF_PIN(gfx); VF_PIN(gfy);
 #undef VF_PIN
 
     unsigned long long t_task = 0ull;
@@ -411,9 +439,11 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         if (TMA) { vf_mbar_wait(&w.mbar[stage], (parity >> stage) & 1u); parity ^= 1u << stage; }
         if (dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tp1) :: "memory");
 
-        int32_t pX = 0, pY = 0, pXn = 0, pYn = 0;          // previous row: own vertex and right neighbour
+        // previous row: raw snapped position (vf_gm_raw) of the lane's vertex and of its right neighbour, their keys
+        int32_t pX = 0, pY = 0, pXn = 0, pYn = 0;
+        uint32_t pK = 0u, pKn = 0u;
         float pZ = 0.0f, pZn = 0.0f;
-        uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the guard band)
+        uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the fast guard band)
         const float* texel = &w.dem[stage][((strip * VF_GM_QCOLS) & 3u) + lane];
         const float* gtexel = dem + ax_tx;
         if (nxt < ntasks) fetch_axes(nstrip, nj0);          // used at the start of the next task
@@ -449,66 +479,82 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
             return r;
         };
-        auto clip_pos2 = [&](uint32_t rr, float ca[4], float cb[4]) {
-            if (SHIPPED) { clip_pos(rr, load_h(rr), ca); clip_pos(rr + 1u, load_h(rr + 1u), cb); return; }
+        auto add2 = [](unsigned long long a, unsigned long long b) -> unsigned long long {
+            unsigned long long r;
+            asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+            return r;
+        };
+        auto lo32 = [](unsigned long long v) -> float { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return a; };
+        auto hi32 = [](unsigned long long v) -> float { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return b; };
+        // Two rows at once.  x and y of ONE vertex travel as a pair (clip x|y, then the raw snapped X|Y: adjacent
+        // registers, which is what the 16-byte ring stores and the key's PRMT want); z and w pair up ACROSS the two rows.
+        // Every component sees the operations of clip_pos in the same order.
+        auto clip_pos2 = [&](uint32_t rr, unsigned long long& cxyA, unsigned long long& cxyB, float& czA, float& cwA, float& czB, float& cwB) {
+            if (SHIPPED) {
+                float ca[4], cb[4];
+                clip_pos(rr, load_h(rr), ca); clip_pos(rr + 1u, load_h(rr + 1u), cb);
+                cxyA = pk(ca[0], ca[1]); cxyB = pk(cb[0], cb[1]); czA = ca[2]; cwA = ca[3]; czB = cb[2]; cwB = cb[3];
+                return;
+            }
             const unsigned long long wy = mul2(pk(load_h(rr), load_h(rr + 1u)), pk(exag, exag));
-            const unsigned long long wz = pk(w.wz[rr], w.wz[rr + 1u]);
-            const unsigned long long v0 = fma2(pk(V4, V4), wy, fma2(pk(V8, V8), wz, pk(a0, a0)));
-            const unsigned long long v1 = fma2(pk(V5, V5), wy, fma2(pk(V9, V9), wz, pk(a1, a1)));
-            const unsigned long long v2 = fma2(pk(V6, V6), wy, fma2(pk(V10, V10), wz, pk(a2, a2)));
-            const unsigned long long c0 = mul2(pk(P0, P0), v0), c1 = mul2(pk(P5, P5), v1);
+            const float wyA = lo32(wy), wyB = hi32(wy), wzA = w.wz[rr], wzB = w.wz[rr + 1u];
+            const unsigned long long V45 = pk(V4, V5), V89 = pk(V8, V9), a01 = pk(a0, a1);
+            const unsigned long long v01A = fma2(V45, pk(wyA, wyA), fma2(V89, pk(wzA, wzA), a01));
+            const unsigned long long v01B = fma2(V45, pk(wyB, wyB), fma2(V89, pk(wzB, wzB), a01));
+            const unsigned long long v2 = fma2(pk(V6, V6), wy, fma2(pk(V10, V10), pk(wzA, wzB), pk(a2, a2)));
+            cxyA = mul2(pk(P0, P5), v01A); cxyB = mul2(pk(P0, P5), v01B);
             // (the additions stay scalar: ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into one FFMA2, which
             // would round P14 + P10 v2 once instead of twice)
             const unsigned long long m2 = mul2(pk(P10, P10), v2), m3 = mul2(pk(P11, P11), v2);
-            float m2a, m2b, m3a, m3b;
-            asm("mov.b64 {%0, %1}, %2;" : "=f"(ca[0]), "=f"(cb[0]) : "l"(c0));
-            asm("mov.b64 {%0, %1}, %2;" : "=f"(ca[1]), "=f"(cb[1]) : "l"(c1));
-            asm("mov.b64 {%0, %1}, %2;" : "=f"(m2a), "=f"(m2b) : "l"(m2));
-            asm("mov.b64 {%0, %1}, %2;" : "=f"(m3a), "=f"(m3b) : "l"(m3));
-            ca[2] = __fadd_rn(P14, m2a); cb[2] = __fadd_rn(P14, m2b);
-            ca[3] = __fadd_rn(P15, m3a); cb[3] = __fadd_rn(P15, m3b);
+            czA = __fadd_rn(P14, lo32(m2)); czB = __fadd_rn(P14, hi32(m2));
+            cwA = __fadd_rn(P15, lo32(m3)); cwB = __fadd_rn(P15, hi32(m3));
         };
-        // viewport + snap (vf_to_screen) given 1/w
+        // inside near / far and the fast guard band: the vertex can be projected and snapped in raw form
+        auto fast_in = [&](const float c[4]) -> bool {
+            return (c[3] > 0.0f) & (c[2] >= 0.0f) & (c[2] <= c[3]) &
+                   (fabsf(c[0]) <= __fmul_rn(gfx, c[3])) & (fabsf(c[1]) <= __fmul_rn(gfy, c[3]));
+        };
+        // viewport + raw snap (vf_to_screen, see vf_gm_raw above) given 1/w.  fma(xn, hw, hw) * 256 == fma(xn, 256 hw,
+        // 256 hw) (scaling by a power of two commutes with the rounding; 256 hw is exact, the sum is never subnormal),
+        // and negating both constants negates the result exactly.
         auto snap = [&](const float c[4], float invw, int32_t& X, int32_t& Y, float& Z) {
             const float xn = __fmul_rn(c[0], invw), yn = __fmul_rn(c[1], invw);
-            // fma(xn, hw, hw) * 256 == fma(xn, 256 hw, 256 hw): scaling by a power of two commutes with the
-            // rounding (256 hw is exact, the sum is never subnormal: it is 0 or at least hw 2^-24)
-            X = __float2int_rn(fmaf(xn, hw, hw));
-            Y = __float2int_rn(fmaf(-yn, hh, hh));
+            X = __float_as_int(__fadd_rn(fmaf(xn, -hw, -hw), VF_GM_MAGIC));      // raw of -X
+            Y = __float_as_int(__fadd_rn(fmaf(yn, hh, -hh), VF_GM_MAGIC));       // raw of -Y  (Y = rint(fma(-yn, hh, hh)))
             Z = DEPTH ? __fmul_rn(c[2], invw) : 0.0f;
         };
         // Branch-free: every lane computes a slot, the stores are predicated (asm: the compiler would put
-        // the five stores behind a divergent branch, and branch resolution is a sixth of this kernel's stalls).
-        static_assert(VF_GM_QCAP * sizeof(int2) == 512, "offsets of the predicated stores below");
+        // the stores behind a divergent branch, and branch resolution is a sixth of this kernel's stalls).
+        static_assert(VF_GM_QCAP * sizeof(int4) == 1024, "offsets of the predicated stores below");
         auto append = [&](uint32_t m, bool keep, uint32_t cell, int32_t aX, int32_t aY, float aZ, int32_t bX, int32_t bY, float bZ,
                           int32_t cX, int32_t cY, float cZ, int32_t dX, int32_t dY, float dZ) {
-            const uint32_t s = (q.qhead + q.qn + __popc(m & below)) & (VF_GM_QCAP - 1u);
+            const uint32_t s4 = ((q.qhead + q.qn + __popc(m & below)) << 2) & (4u * VF_GM_QCAP - 4u);   // slot * 4
+            const uint32_t s = s4 >> 2;
             asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t"
-                         "@p st.shared.v2.b32 [%1], {%3, %4};\n\t@p st.shared.v2.b32 [%1+512], {%5, %6};\n\t"
-                         "@p st.shared.v2.b32 [%1+1024], {%7, %8};\n\t@p st.shared.v2.b32 [%1+1536], {%9, %10};\n\t"
+                         "@p st.shared.v4.b32 [%1], {%3, %4, %5, %6};\n\t@p st.shared.v4.b32 [%1+1024], {%7, %8, %9, %10};\n\t"
                          "@p st.shared.b32 [%2], %11;\n\t}"
-                         :: "r"((uint32_t)keep), "r"(qv_base + s * 8u), "r"(qcell_base + s * 4u), "r"(aX), "r"(aY), "r"(bX), "r"(bY),
+                         :: "r"((uint32_t)keep), "r"(qv_base + s4 * 4u), "r"(qcell_base + s4), "r"(aX), "r"(aY), "r"(bX), "r"(bY),
                             "r"(cX), "r"(cY), "r"(dX), "r"(dY), "r"(cell) : "memory");
             if (DEPTH && keep) { w.qz[0][s] = aZ; w.qz[1][s] = bZ; w.qz[2][s] = cZ; w.qz[3][s] = dZ; }
             q.qn += (uint32_t)__popc(m);
         };
 
         // One vertex row, general form: tracks the clip state of the vertices; cells with a vertex
-        // outside the guard band are queued for a rebuild from scratch.
+        // outside the (fast) guard band are queued for a rebuild from scratch.
         auto row = [&]() {
             float c[4];
             clip_pos(r, load_h(r), c);
-            const bool in = vf_clip_in(c) || !colv;
+            const bool in = fast_in(c) || !colv;
             int32_t X, Y;
             float Z;
             snap(c, __frcp_rn(c[3]), X, Y, Z);
+            const uint32_t K = vf_gm_key(X, Y);
             const int32_t Xn = __shfl_down_sync(0xffffffffu, X, 1), Yn = __shfl_down_sync(0xffffffffu, Y, 1);
+            const uint32_t Kn = vf_gm_key(Xn, Yn);
             float Zn = 0.0f;
             if (DEPTH) Zn = __shfl_down_sync(0xffffffffu, Z, 1);
-            // no pixel centre inside the cell's bbox -> neither triangle draws (off-screen cells die in the drain)
-            bool keep = cellv && r > 0u &&
-                        vf_span_has_centre(min(min(pX, pXn), min(X, Xn)), max(max(pX, pXn), max(X, Xn))) &&
-                        vf_span_has_centre(min(min(pY, pYn), min(Y, Yn)), max(max(pY, pYn), max(Y, Yn)));
+            // the four vertices share a pixel-centre index on one axis -> neither triangle draws (off-screen cells die in the drain)
+            bool keep = vf_gm_cell_live(vf_gm_keydiff(pK, pKn, K, Kn), cellv && r > 0u);
             uint32_t rebuild = 0u;
             const uint32_t nin = __ballot_sync(0xffffffffu, !in);
             uint32_t st = 0u, stn = 0u;
@@ -525,70 +571,55 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             pst = st; pstn = stn; pnin = nin;
             const uint32_t m = __ballot_sync(0xffffffffu, keep);
             append(m, keep, (cell0 + r * gm) | rebuild, pX, pY, pZ, pXn, pYn, pZn, X, Y, Z, Xn, Yn, Zn);
-            pX = X; pY = Y; pXn = Xn; pYn = Yn; pZ = Z; pZn = Zn;
+            pX = X; pY = Y; pXn = Xn; pYn = Yn; pK = K; pKn = Kn; pZ = Z; pZn = Zn;
             ++r;
         };
 
         // Two vertex rows at once, straight-line (the two vertex stages interleave): taken while
-        // every vertex is inside the guard band with w in [2^-100, 2^100], where rcp.rn is
+        // every vertex is inside the fast guard band with w in [2^-100, 2^100], where rcp.rn is
         // MUFU.RCP + one Newton step.  Returns false (nothing consumed) when that does not hold.
         auto row_pair = [&]() -> bool {
-            float ca[4], cb[4];
-#ifdef VF_GM_NO_F32X2
-            clip_pos(r, load_h(r), ca);
-            clip_pos(r + 1u, load_h(r + 1u), cb);
-#else
-            clip_pos2(r, ca, cb);
-#endif
-            const float ga = __fmul_rn(VF_GUARD_K, ca[3]), gb = __fmul_rn(VF_GUARD_K, cb[3]);
-            const bool oka = (ca[3] >= 0x1p-100f) & (ca[3] <= 0x1p100f) & (ca[2] >= 0.0f) & (ca[2] <= ca[3]) &
-                             (fabsf(ca[0]) <= ga) & (fabsf(ca[1]) <= ga);
-            const bool okb = (cb[3] >= 0x1p-100f) & (cb[3] <= 0x1p100f) & (cb[2] >= 0.0f) & (cb[2] <= cb[3]) &
-                             (fabsf(cb[0]) <= gb) & (fabsf(cb[1]) <= gb);
+            unsigned long long cxyA, cxyB;
+            float czA, cwA, czB, cwB;
+            clip_pos2(r, cxyA, cxyB, czA, cwA, czB, cwB);
+            const unsigned long long g2 = pk(gfx, gfy);
+            const unsigned long long gA = mul2(g2, pk(cwA, cwA)), gB = mul2(g2, pk(cwB, cwB));
+            const bool oka = (cwA >= 0x1p-100f) & (cwA <= 0x1p100f) & (czA >= 0.0f) & (czA <= cwA) &
+                             (fabsf(lo32(cxyA)) <= lo32(gA)) & (fabsf(hi32(cxyA)) <= hi32(gA));
+            const bool okb = (cwB >= 0x1p-100f) & (cwB <= 0x1p100f) & (czB >= 0.0f) & (czB <= cwB) &
+                             (fabsf(lo32(cxyB)) <= lo32(gB)) & (fabsf(hi32(cxyB)) <= hi32(gB));
             if (__any_sync(0xffffffffu, colv & !(oka & okb))) return false;
             float ra, rb;
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(ca[3]));
-            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cb[3]));
-            ra = fmaf(ra, -fmaf(ca[3], ra, -1.0f), ra);
-            rb = fmaf(rb, -fmaf(cb[3], rb, -1.0f), rb);
-            int32_t XA, YA, XB, YB;
-            float ZA, ZB;
-#ifdef VF_GM_NO_F32X2
-            snap(ca, ra, XA, YA, ZA);
-            snap(cb, rb, XB, YB, ZB);
-#else
-            {   // snap of both rows, packed: fma(-yn, hh, hh) == fma(yn, -hh, hh)
-                const unsigned long long r2 = pk(ra, rb);
-                const unsigned long long x2 = fma2(mul2(pk(ca[0], cb[0]), r2), pk(hw, hw), pk(hw, hw));
-                const unsigned long long y2 = fma2(mul2(pk(ca[1], cb[1]), r2), pk(-hh, -hh), pk(hh, hh));
-                float xa, xb, ya, yb;
-                asm("mov.b64 {%0, %1}, %2;" : "=f"(xa), "=f"(xb) : "l"(x2));
-                asm("mov.b64 {%0, %1}, %2;" : "=f"(ya), "=f"(yb) : "l"(y2));
-                XA = __float2int_rn(xa); XB = __float2int_rn(xb);
-                YA = __float2int_rn(ya); YB = __float2int_rn(yb);
-                ZA = DEPTH ? __fmul_rn(ca[2], ra) : 0.0f; ZB = DEPTH ? __fmul_rn(cb[2], rb) : 0.0f;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(cwA));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cwB));
+            ra = fmaf(ra, -fmaf(cwA, ra, -1.0f), ra);
+            rb = fmaf(rb, -fmaf(cwB, rb, -1.0f), rb);
+            int32_t XA, YA, XB, YB;                         // raw (vf_gm_raw)
+            {   // raw snap: (xn, yn) = clip (x, y) / w; (-X, -Y) = fma((xn, yn), (-hw, hh), (-hw, -hh)); + magic
+                const unsigned long long sc = pk(-hw, hh), of = pk(-hw, -hh), mg = pk(VF_GM_MAGIC, VF_GM_MAGIC);
+                const unsigned long long xyA = add2(fma2(mul2(cxyA, pk(ra, ra)), sc, of), mg);
+                const unsigned long long xyB = add2(fma2(mul2(cxyB, pk(rb, rb)), sc, of), mg);
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(XA), "=r"(YA) : "l"(xyA));
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(XB), "=r"(YB) : "l"(xyB));
             }
-#endif
+            const float ZA = DEPTH ? __fmul_rn(czA, ra) : 0.0f, ZB = DEPTH ? __fmul_rn(czB, rb) : 0.0f;
+            const uint32_t KA = vf_gm_key(XA, YA), KB = vf_gm_key(XB, YB);
             const int32_t XAn = __shfl_down_sync(0xffffffffu, XA, 1), YAn = __shfl_down_sync(0xffffffffu, YA, 1);
             const int32_t XBn = __shfl_down_sync(0xffffffffu, XB, 1), YBn = __shfl_down_sync(0xffffffffu, YB, 1);
+            const uint32_t KAn = vf_gm_key(XAn, YAn), KBn = vf_gm_key(XBn, YBn);
             float ZAn = 0.0f, ZBn = 0.0f;
             if (DEPTH) { ZAn = __shfl_down_sync(0xffffffffu, ZA, 1); ZBn = __shfl_down_sync(0xffffffffu, ZB, 1); }
-            const int32_t eAx0 = min(XA, XAn), eAx1 = max(XA, XAn), eAy0 = min(YA, YAn), eAy1 = max(YA, YAn);   // edge of row A
-            const bool keepA = cellv &
-                vf_span_has_centre(min(min(pX, pXn), eAx0), max(max(pX, pXn), eAx1)) &
-                vf_span_has_centre(min(min(pY, pYn), eAy0), max(max(pY, pYn), eAy1));
-            const bool keepB = cellv &
-                vf_span_has_centre(min(min(XB, XBn), eAx0), max(max(XB, XBn), eAx1)) &
-                vf_span_has_centre(min(min(YB, YBn), eAy0), max(max(YB, YBn), eAy1));
+            const bool keepA = vf_gm_cell_live(vf_gm_keydiff(KA, KAn, pK, pKn), cellv);
+            const bool keepB = vf_gm_cell_live(vf_gm_keydiff(KA, KAn, KB, KBn), cellv);
             const uint32_t mA = __ballot_sync(0xffffffffu, keepA), mB = __ballot_sync(0xffffffffu, keepB);
             append(mA, keepA, cell0 + r * gm, pX, pY, pZ, pXn, pYn, pZn, XA, YA, ZA, XAn, YAn, ZAn);
             if (q.qn + (uint32_t)__popc(mB) > VF_GM_QCAP) {      // ring full (coarse grids): row B is redone after the drain
-                pX = XA; pY = YA; pXn = XAn; pYn = YAn; pZ = ZA; pZn = ZAn;
+                pX = XA; pY = YA; pXn = XAn; pYn = YAn; pK = KA; pKn = KAn; pZ = ZA; pZn = ZAn;
                 r += 1u;
                 return true;
             }
             append(mB, keepB, cell0 + (r + 1u) * gm, XA, YA, ZA, XAn, YAn, ZAn, XB, YB, ZB, XBn, YBn, ZBn);
-            pX = XB; pY = YB; pXn = XBn; pYn = YBn; pZ = ZB; pZn = ZBn;
+            pX = XB; pY = YB; pXn = XBn; pYn = YBn; pK = KB; pKn = KBn; pZ = ZB; pZn = ZBn;
             r += 2u;
             return true;
         };

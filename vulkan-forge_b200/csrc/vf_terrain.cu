@@ -58,7 +58,12 @@ struct vf_scene {
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
     alignas(64) CUtensorMap dem_map_gm[2];  // same tensor, one box per warp task of k_geom_march: [0] 36x31 floats, [1] 36x27 (depth)
-    bool use_tma = false;                // grid == DEM with identity texel mapping
+    // Height of every grid vertex as one G x G image, h_grid[j][i] = dem[ty[j]][tx[i]], built once per upload when the
+    // grid -> texel mapping is not the identity (grid != DEM size; or f32 rounding of u * W near the upper end of large
+    // grids: 7 indices at G = 16384).  The geometry kernels then stage their texels with TMA boxes whatever the sizes;
+    // nullptr = identity, the DEM itself is that image.  The fragment stage always reads the DEM proper.
+    float* d_hgrid = nullptr; float* d_hgrid_back = nullptr; uint32_t hpitch = 0;
+    bool use_tma = false;                // texels of the geometry pass are staged with TMA
     bool geom_tiled = false;             // VF_GEOM_TILED at creation: tiled k_geom instead of k_geom_march (A/B runs)
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
     // front image render; swapped in by the next submit
@@ -107,7 +112,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
     cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag); cudaFree(s->d_segtab);
-    cudaFree(s->d_dem_back);
+    cudaFree(s->d_dem_back); cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
     if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
     if (s->ev_front_released) cudaEventDestroy(s->ev_front_released);
@@ -189,6 +194,18 @@ static bool scene_encode_maps(float* d_dem, uint32_t w, uint32_t h, uint32_t pit
 
 static void scene_resolve_readers(vf_scene* s, const float* image);
 
+// h_grid[j][i] = dem[ty[j]][tx[i]] (nearest / clamp sampler of src/scene/mod.rs:263-268 applied once per upload)
+__global__ void __launch_bounds__(256)
+k_resample(const VfAxis* __restrict__ axis, const float* __restrict__ dem, uint32_t dem_pitch, uint32_t G, uint32_t hpitch,
+           float* __restrict__ hgrid) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= G) return;
+    const int tx = axis[i].tx;
+    for (uint32_t j = blockIdx.y; j < G; j += gridDim.y)
+        hgrid[(size_t)j * hpitch + i] = __ldg(dem + (size_t)axis[j].ty * dem_pitch + tx);
+}
+static void launch_resample(const vf_scene* s, const float* dem, float* hgrid, cudaStream_t st);
+
 // every entry point works on the scene's own device, whatever vf_init selected since its creation
 static int scene_bind(const vf_scene* s) {
     if (!s) return vf_set_error(VF_E_INVALID, "null scene");
@@ -214,25 +231,52 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
                               cudaMemcpyHostToDevice, s->stream));
     int rc = scene_rebuild_axis(s);
     if (rc) return rc;
-    // TMA path: every grid index must fetch the texel of the same index (f32 rounding of
-    // u*W can break this near the upper end at large sizes), checked on the device
+    // TMA staging of the geometry pass: over the DEM itself when every grid index fetches the texel of the same
+    // index (checked on the device: f32 rounding of u*W can break it near the upper end at large sizes, SURVEY
+    // 7.3-5), otherwise over the G x G image of vertex heights resampled here once
     s->use_tma = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
     memset(s->dem_map_gm, 0, sizeof s->dem_map_gm);
-    if (s->G == w && s->G == h && tmap_encoder() && !getenv("VF_DISABLE_TMA")) {
-        if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
-        const uint32_t one = 1u;
+    const uint64_t hbytes = (uint64_t)((s->G + 3u) & ~3u) * s->G * 4u;
+    if (tmap_encoder() && !getenv("VF_DISABLE_TMA") && hbytes <= (8ull << 30)) {
         uint32_t flag = 0u;
-        VF_CUDA(cudaMemcpyAsync(s->d_flag, &one, 4, cudaMemcpyHostToDevice, s->stream));
-        k_axis_identity<<<(s->G + 255) / 256, 256, 0, s->stream>>>(s->d_axis, s->G, s->d_flag);
-        VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
-        VF_CUDA(cudaStreamSynchronize(s->stream));
-        if (flag == 1u) {
-            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, s->dem_map_gm);
+        if (s->G == w && s->G == h) {
+            if (!s->d_flag) VF_CUDA(cudaMalloc(&s->d_flag, 4));
+            const uint32_t one = 1u;
+            VF_CUDA(cudaMemcpyAsync(s->d_flag, &one, 4, cudaMemcpyHostToDevice, s->stream));
+            k_axis_identity<<<(s->G + 255) / 256, 256, 0, s->stream>>>(s->d_axis, s->G, s->d_flag);
+            VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
+            VF_CUDA(cudaStreamSynchronize(s->stream));
         }
+        if (flag == 1u) {
+            cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
+            s->d_hgrid = s->d_hgrid_back = nullptr; s->hpitch = 0;
+            s->use_tma = scene_encode_maps(s->d_dem, w, h, pitch, &s->dem_map, s->dem_map_gm);
+        } else {
+            const uint32_t hp = (s->G + 3u) & ~3u;
+            if (!s->d_hgrid || s->hpitch != hp) {
+                cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
+                s->d_hgrid = s->d_hgrid_back = nullptr; s->back_valid = false;
+                if (cudaMalloc(&s->d_hgrid, hbytes) != cudaSuccess) { (void)cudaGetLastError(); s->d_hgrid = nullptr; }
+                s->hpitch = hp;
+            }
+            if (s->d_hgrid) {
+                launch_resample(s, s->d_dem, s->d_hgrid, s->stream);
+                VF_CUDA(cudaGetLastError());
+                s->use_tma = scene_encode_maps(s->d_hgrid, s->G, s->G, hp, &s->dem_map, s->dem_map_gm);
+            }
+        }
+    } else {
+        cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
+        s->d_hgrid = s->d_hgrid_back = nullptr; s->hpitch = 0;
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
     return VF_OK;
+}
+
+static void launch_resample(const vf_scene* s, const float* dem, float* hgrid, cudaStream_t st) {
+    const uint32_t gy = std::min<uint32_t>(s->G, 4096u);
+    k_resample<<<dim3((s->G + 255) / 256, gy), 256, 0, st>>>(s->d_axis, dem, s->pitch, s->G, s->hpitch, hgrid);
 }
 
 extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_unorm, vf_scene** out) {
@@ -549,7 +593,7 @@ static int scene_apply_pending_dem(vf_scene* s) {
     VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_uploaded, 0));
     VF_CUDA(cudaEventRecord(s->ev_front_released, s->stream));   // every frame of the old image precedes this
     s->front_released_once = true;
-    std::swap(s->d_dem, s->d_dem_back);
+    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back);
     std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
     s->back_pending = false;
     return VF_OK;
@@ -634,7 +678,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 
 // ---- pipelined interface: uploads and batches overlap across calls -------------------------------
 static void scene_swap_images(vf_scene* s) {
-    std::swap(s->d_dem, s->d_dem_back);
+    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back);
     std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
 }
 
@@ -688,9 +732,14 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
         VF_CUDA(cudaMalloc(&s->d_dem_back, (size_t)pitch * h * 4));
         s->back_valid = false;
     }
+    if (s->d_hgrid && !s->d_hgrid_back) {
+        VF_CUDA(cudaMalloc(&s->d_hgrid_back, (size_t)s->hpitch * s->G * 4));
+        s->back_valid = false;
+    }
     if (!s->back_valid) {
-        if (s->use_tma && !scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, s->dem_map_gm_b))
-            return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
+        const bool ok = !s->use_tma || (s->d_hgrid ? scene_encode_maps(s->d_hgrid_back, s->G, s->G, s->hpitch, &s->dem_map_b, s->dem_map_gm_b)
+                                                   : scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, s->dem_map_gm_b));
+        if (!ok) return vf_set_error(VF_E_CUDA, "tensor map encoding failed for the back height image");
         s->back_valid = true;
     }
     scene_resolve_readers(s, s->d_dem_back);      // normally none: those batches were collected long ago
@@ -698,6 +747,10 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
     if (s->front_released_once) VF_CUDA(cudaStreamWaitEvent(s->upload_stream, s->ev_front_released, 0));
     VF_CUDA(cudaMemcpy2DAsync(s->d_dem_back, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
                               cudaMemcpyHostToDevice, s->upload_stream));
+    if (s->d_hgrid_back) {                        // vertex heights of the new image, behind its upload
+        launch_resample(s, s->d_dem_back, s->d_hgrid_back, s->upload_stream);
+        VF_CUDA(cudaGetLastError());
+    }
     VF_CUDA(cudaEventRecord(s->ev_uploaded, s->upload_stream));
     s->back_pending = true;
     return VF_OK;

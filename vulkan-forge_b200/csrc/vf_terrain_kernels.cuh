@@ -166,9 +166,10 @@ __device__ __forceinline__ void vf_thin_raster(const VfEdges& s, int x0, int x1,
 //                runs on wrapped 32-bit sums (one IADD per edge and step);
 //   flat edges : an edge parallel to the run (amaj == 0) is constant on a line; its exact 64-bit
 //                sign is taken once per line and it is left out of the 32-bit test.
-// emit(covered, idx, m, c, cols) is called for EVERY sample of a run (so that it can be a predicated store
-// instead of a branch) with the sample's index in the W-wide frame and its (line, position on the line);
-// no edge values (depth: vf_edges_at on the covered sample restores them).
+// emit(covered, idx, e0, e1, e2) is called for EVERY sample of a run (so that it can be a predicated store instead
+// of a branch) with the sample's index in the W-wide frame and the low words of the three biased edge values: for a
+// covered sample they ARE the values (0 <= E_i < 2^31), a flat edge included (constant along its line), which is what
+// the depth interpolation needs.
 template <typename Emit>
 __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x1, int y0, int y1, uint32_t W, Emit&& emit) {
     const bool cols = (x1 - x0) <= (y1 - y0);        // minor axis = x: walk columns, runs along y
@@ -188,8 +189,10 @@ __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x
         const float mg = fmaf(fmaf((float)nmin, fabsf(sl), fabsf(t0)), 0x1p-20f, 0.015625f);
         tc0[i] = lower[i] ? __fsub_rn(t0, mg) : __fadd_rn(t0, mg);
         slope[i] = sl;
-        e32[i] = amaj != 0 ? (uint32_t)s.E[i] : 0u;
-        smin[i] = amaj != 0 ? (uint32_t)amin * (uint32_t)VF_SUBPIX : 0u;
+        // a flat edge takes part too: on a line that is not dead it is >= 0 and, like the others, below 2^31 wherever
+        // the run is not empty, so its low word is exact and cannot change the sign of the OR
+        e32[i] = (uint32_t)s.E[i];
+        smin[i] = (uint32_t)amin * (uint32_t)VF_SUBPIX;
         smaj[i] = (uint32_t)amaj * (uint32_t)VF_SUBPIX;
     }
     for (int m = 0; m < nmin; ++m) {
@@ -217,11 +220,11 @@ __device__ __forceinline__ void vf_thin_raster32(const VfEdges& s, int x0, int x
         // sample index in the frame, stepped along the run (W per sample down a column, 1 along a row)
         uint32_t idx = cols ? (uint32_t)(y0 + c0) * W + (uint32_t)(x0 + m) : (uint32_t)(y0 + m) * W + (uint32_t)(x0 + c0);
         int c = c0;
-        emit(c <= c1 && (int32_t)(ed0 | ed1 | ed2) >= 0, idx, m, c, cols);       // most runs hold one sample or none: no branch
+        emit(c <= c1 && (int32_t)(ed0 | ed1 | ed2) >= 0, idx, ed0, ed1, ed2);    // most runs hold one sample or none: no branch
         while (++c <= c1) {
             ed0 += smaj[0]; ed1 += smaj[1]; ed2 += smaj[2];
             idx += istep;
-            emit((int32_t)(ed0 | ed1 | ed2) >= 0, idx, m, c, cols);
+            emit((int32_t)(ed0 | ed1 | ed2) >= 0, idx, ed0, ed1, ed2);
         }
     }
 }

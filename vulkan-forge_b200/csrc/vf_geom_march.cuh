@@ -310,7 +310,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
              const VfAxis* __restrict__ axis, const float* __restrict__ dem,
              unsigned long long* __restrict__ vis, uint32_t* __restrict__ big_prims, uint32_t big_capacity,
              uint32_t* __restrict__ counters, const uint2* __restrict__ segtab, uint32_t nsegs, uint32_t nfull, uint32_t rows_full,
-             unsigned long long* __restrict__ dbg) {
+             const float2* __restrict__ hmm, uint32_t hmm_nb, unsigned long long* __restrict__ dbg) {
     extern __shared__ __align__(128) unsigned char vf_gm_smem[];
 #ifndef VF_GM_PROFILE                                       // the timing dump costs registers: only in -DVF_GM_PROFILE builds
     dbg = nullptr;
@@ -392,10 +392,31 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(az_ty) : "l"(&pz->ty));
         }
     };
+    // Height bounds of a task (vf_terrain.cu: k_hminmax, (min, max) of every 32 x 32 block of vertex heights): lanes
+    // 0..3 fetch the <= 2 x 2 blocks the task's 32 x 31 vertices touch, one task ahead like the axis entries.
+    float mm_lo = __int_as_float(0x7f800000), mm_hi = __int_as_float(0xff800000);
+    auto fetch_mm = [&](uint32_t s0, uint32_t r0, uint32_t rows) {
+        if (hmm != nullptr && lane < 4u) {
+            const uint32_t c0 = s0 * VF_GM_QCOLS;
+            const uint32_t bi = min((c0 >> 5) + (lane & 1u), min(c0 + 31u, gm) >> 5);
+            const uint32_t bj = min((r0 >> 5) + (lane >> 1), min(r0 + rows, gm) >> 5);
+            asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(mm_lo), "=f"(mm_hi) : "l"(hmm + (size_t)bj * hmm_nb + bi));
+        }
+    };
     if (cur < ntasks) {
         decode(cur, strip, j0, nr);
         issue(true, strip, j0, 0u);
         fetch_axes(strip, j0);
+        fetch_mm(strip, j0, nr);
+    }
+    // magnitude of the view / projection entries the vertex stage uses: scale of the safety margin below
+    float vp_scale;
+    {
+        float vmax = 1.0f, pmax = 1.0f;
+#pragma unroll
+        for (int k = 0; k < 15; ++k) if ((k & 3) != 3) vmax = fmaxf(vmax, fabsf(f.V[k]));
+        pmax = fmaxf(pmax, fmaxf(fmaxf(fabsf(f.P[0]), fabsf(f.P[5])), fmaxf(fmaxf(fabsf(f.P[10]), fabsf(f.P[11])), fmaxf(fabsf(f.P[14]), fabsf(f.P[15])))));
+        vp_scale = __fmul_rn(__fmul_rn(vmax, pmax), 1e-4f);
     }
     // frame constants of the row loop, pinned in registers (otherwise every use re-reads the constant bank)
     float V4 = f.V[4], V5 = f.V[5], V6 = f.V[6], V8 = f.V[8], V9 = f.V[9], V10 = f.V[10];
@@ -417,6 +438,33 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         float wx, wz_lane;
         asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(wx) : "f"(ax_coord), "f"(f.spacing));
         asm volatile("mul.rn.f32 %0, %1, %2;" : "=f"(wz_lane) : "f"(az_coord), "f"(f.spacing));
+        // Is every vertex of this task inside near / far / the fast guard band with w in rcp's fast range?  Clip
+        // coordinates are affine in (x, height, z), the conditions are linear in clip coordinates, so they hold on the
+        // task's box [x0, x1] x [hmin, hmax] x [z0, z1] if they hold at its 8 corners -- checked by lanes 0..7 with a
+        // margin far above the rounding error of the float evaluation (1e-4 of the magnitude of the terms).  A safe
+        // task runs the row pairs without the per-vertex tests.
+        bool task_safe = false;
+        if (hmm != nullptr) {
+            float lo = mm_lo, hi = mm_hi;
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, 1)); hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, 1));
+            lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, 2)); hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, 2));
+            lo = __shfl_sync(0xffffffffu, lo, 0); hi = __shfl_sync(0xffffffffu, hi, 0);
+            const float cxw = __shfl_sync(0xffffffffu, wx, (lane & 1u) ? 31u : 0u);
+            const float czw = __shfl_sync(0xffffffffu, wz_lane, (lane & 2u) ? min(nr, VROWS - 1u) : 0u);
+            float hc = (lane & 4u) ? hi : lo;
+            if (SHIPPED) hc = __fadd_rn(hc, (lane & 4u) ? 0.5f : -0.5f);          // analytic term: |0.25 sin + 0.25 cos| <= 0.5
+            const float cwy = __fmul_rn(hc, f.exag);
+            const float v0 = fmaf(f.V[4], cwy, fmaf(f.V[8], czw, fmaf(f.V[0], cxw, f.V[12])));
+            const float v1 = fmaf(f.V[5], cwy, fmaf(f.V[9], czw, fmaf(f.V[1], cxw, f.V[13])));
+            const float v2 = fmaf(f.V[6], cwy, fmaf(f.V[10], czw, fmaf(f.V[2], cxw, f.V[14])));
+            const float c0 = __fmul_rn(f.P[0], v0), c1 = __fmul_rn(f.P[5], v1);
+            const float c2 = __fadd_rn(f.P[14], __fmul_rn(f.P[10], v2)), c3 = __fadd_rn(f.P[15], __fmul_rn(f.P[11], v2));
+            const float mg = __fmul_rn(vp_scale, __fadd_rn(__fadd_rn(fabsf(cxw), fabsf(cwy)), __fadd_rn(fabsf(czw), 1.0f)));
+            const bool okc = (c3 >= __fadd_rn(mg, 1e-30f)) & (c3 <= 1e30f) & (c2 >= mg) & (__fsub_rn(c3, c2) >= mg) &
+                             (__fsub_rn(__fmul_rn(__fmul_rn(gfx, 0.999f), c3), fabsf(c0)) >= mg) &
+                             (__fsub_rn(__fmul_rn(__fmul_rn(gfy, 0.999f), c3), fabsf(c1)) >= mg) & (hi < 1e30f) & (lo > -1e30f);
+            task_safe = (__ballot_sync(0xffffffffu, okc) & 0xffu) == 0xffu;
+        }
         uint32_t nstrip = 0u, nj0 = 0u, nnr = 0u;           // place of `nxt`
         if (nxt < ntasks) decode(nxt, nstrip, nj0, nnr);
         issue(nxt < ntasks, nstrip, nj0, stage ^ 1u);
@@ -446,7 +494,7 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         uint32_t pst = 0u, pstn = 0u, pnin = 0u;           // clip state of the previous row (0 = inside the fast guard band)
         const float* texel = &w.dem[stage][((strip * VF_GM_QCOLS) & 3u) + lane];
         const float* gtexel = dem + ax_tx;
-        if (nxt < ntasks) fetch_axes(nstrip, nj0);          // used at the start of the next task
+        if (nxt < ntasks) { fetch_axes(nstrip, nj0); fetch_mm(nstrip, nj0, nnr); }   // used at the start of the next task
         const uint32_t cell0 = (j0 - 1u) * gm + i;          // cell index of (row r-1, column i) is cell0 + r*gm
         uint32_t r = 0u;
         auto load_h = [&](uint32_t rr) -> float {
@@ -578,17 +626,20 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
         // Two vertex rows at once, straight-line (the two vertex stages interleave): taken while
         // every vertex is inside the fast guard band with w in [2^-100, 2^100], where rcp.rn is
         // MUFU.RCP + one Newton step.  Returns false (nothing consumed) when that does not hold.
-        auto row_pair = [&]() -> bool {
+        auto row_pair = [&](auto checked_tag) -> bool {
+            constexpr bool CHECKED = decltype(checked_tag)::value;       // false: the task passed the corner test above
             unsigned long long cxyA, cxyB;
             float czA, cwA, czB, cwB;
             clip_pos2(r, cxyA, cxyB, czA, cwA, czB, cwB);
-            const unsigned long long g2 = pk(gfx, gfy);
-            const unsigned long long gA = mul2(g2, pk(cwA, cwA)), gB = mul2(g2, pk(cwB, cwB));
-            const bool oka = (cwA >= 0x1p-100f) & (cwA <= 0x1p100f) & (czA >= 0.0f) & (czA <= cwA) &
-                             (fabsf(lo32(cxyA)) <= lo32(gA)) & (fabsf(hi32(cxyA)) <= hi32(gA));
-            const bool okb = (cwB >= 0x1p-100f) & (cwB <= 0x1p100f) & (czB >= 0.0f) & (czB <= cwB) &
-                             (fabsf(lo32(cxyB)) <= lo32(gB)) & (fabsf(hi32(cxyB)) <= hi32(gB));
-            if (__any_sync(0xffffffffu, colv & !(oka & okb))) return false;
+            if (CHECKED) {
+                const unsigned long long g2 = pk(gfx, gfy);
+                const unsigned long long gA = mul2(g2, pk(cwA, cwA)), gB = mul2(g2, pk(cwB, cwB));
+                const bool oka = (cwA >= 0x1p-100f) & (cwA <= 0x1p100f) & (czA >= 0.0f) & (czA <= cwA) &
+                                 (fabsf(lo32(cxyA)) <= lo32(gA)) & (fabsf(hi32(cxyA)) <= hi32(gA));
+                const bool okb = (cwB >= 0x1p-100f) & (cwB <= 0x1p100f) & (czB >= 0.0f) & (czB <= cwB) &
+                                 (fabsf(lo32(cxyB)) <= lo32(gB)) & (fabsf(hi32(cxyB)) <= hi32(gB));
+                if (__any_sync(0xffffffffu, colv & !(oka & okb))) return false;
+            }
             float ra, rb;
             asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(cwA));
             asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cwB));
@@ -624,6 +675,55 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             return true;
         };
 
+        // Four vertex rows at once, for tasks that passed the corner test (no per-vertex tests, so nothing can send the
+        // rows back): the two pairs are independent up to the appends, which gives the scheduler two dependence chains
+        // to interleave (the kernel waits on fixed-latency dependences with its 4 warps per scheduler).  Returns false,
+        // with nothing consumed, when the ring could not take the four rows' cells.
+        auto row_quad = [&]() -> bool {
+            int32_t X[4], Y[4], Xn[4], Yn[4];
+            float Z[4], Zn[4];
+            uint32_t K[4], Kn[4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                unsigned long long cxyA, cxyB;
+                float czA, cwA, czB, cwB, ra, rb;
+                clip_pos2(r + 2u * h, cxyA, cxyB, czA, cwA, czB, cwB);
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ra) : "f"(cwA));
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rb) : "f"(cwB));
+                ra = fmaf(ra, -fmaf(cwA, ra, -1.0f), ra);
+                rb = fmaf(rb, -fmaf(cwB, rb, -1.0f), rb);
+                const unsigned long long sc = pk(-hw, hh), of = pk(-hw, -hh), mg = pk(VF_GM_MAGIC, VF_GM_MAGIC);
+                const unsigned long long xyA = add2(fma2(mul2(cxyA, pk(ra, ra)), sc, of), mg);
+                const unsigned long long xyB = add2(fma2(mul2(cxyB, pk(rb, rb)), sc, of), mg);
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(X[2 * h]), "=r"(Y[2 * h]) : "l"(xyA));
+                asm("mov.b64 {%0, %1}, %2;" : "=r"(X[2 * h + 1]), "=r"(Y[2 * h + 1]) : "l"(xyB));
+                Z[2 * h] = DEPTH ? __fmul_rn(czA, ra) : 0.0f; Z[2 * h + 1] = DEPTH ? __fmul_rn(czB, rb) : 0.0f;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                K[k] = vf_gm_key(X[k], Y[k]);
+                Xn[k] = __shfl_down_sync(0xffffffffu, X[k], 1); Yn[k] = __shfl_down_sync(0xffffffffu, Y[k], 1);
+                Kn[k] = vf_gm_key(Xn[k], Yn[k]);
+                Zn[k] = DEPTH ? __shfl_down_sync(0xffffffffu, Z[k], 1) : 0.0f;
+            }
+            bool keep[4];
+            uint32_t m[4];
+            keep[0] = vf_gm_cell_live(vf_gm_keydiff(K[0], Kn[0], pK, pKn), cellv);
+#pragma unroll
+            for (int k = 1; k < 4; ++k) keep[k] = vf_gm_cell_live(vf_gm_keydiff(K[k], Kn[k], K[k - 1], Kn[k - 1]), cellv);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) m[k] = __ballot_sync(0xffffffffu, keep[k]);
+            if (q.qn + (uint32_t)(__popc(m[0]) + __popc(m[1]) + __popc(m[2]) + __popc(m[3])) > VF_GM_QCAP) return false;
+            append(m[0], keep[0], cell0 + r * gm, pX, pY, pZ, pXn, pYn, pZn, X[0], Y[0], Z[0], Xn[0], Yn[0], Zn[0]);
+#pragma unroll
+            for (int k = 1; k < 4; ++k)
+                append(m[k], keep[k], cell0 + (r + k) * gm, X[k - 1], Y[k - 1], Z[k - 1], Xn[k - 1], Yn[k - 1], Zn[k - 1],
+                       X[k], Y[k], Z[k], Xn[k], Yn[k], Zn[k]);
+            pX = X[3]; pY = Y[3]; pXn = Xn[3]; pYn = Yn[3]; pK = K[3]; pKn = Kn[3]; pZ = Z[3]; pZn = Zn[3];
+            r += 4u;
+            return true;
+        };
+
         row();                                              // row 0 primes the previous-row registers
         if (dbg) {
             tp2 = (unsigned long long)pX & 1ull;            // the stamp waits for the row's results
@@ -641,9 +741,19 @@ k_geom_march(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensor
             // after a row with a vertex outside the guard band the general routine runs until a
             // row is clean again (pnin == 0 implies pst == pstn == 0)
             if (fast && pnin == 0u && r + 1u < nrows) {
+                if (task_safe) {
+#ifndef VF_GM_NO_QUAD
 #pragma unroll 1
-                while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
-                    if (!row_pair()) { fast = false; break; }
+                    while (r + 3u < nrows && q.qn <= VF_GM_QCAP - 32u)
+                        if (!row_quad()) row_pair(std::false_type{});       // ring nearly full: advance by a pair, drain below
+#endif
+#pragma unroll 1
+                    while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u) row_pair(std::false_type{});
+                } else {
+#pragma unroll 1
+                    while (r + 1u < nrows && q.qn <= VF_GM_QCAP - 32u)
+                        if (!row_pair(std::true_type{})) { fast = false; break; }
+                }
             } else {
 #pragma unroll 1
                 while (r < nrows && q.qn <= VF_GM_QCAP - 32u) {

@@ -63,6 +63,9 @@ struct vf_scene {
     // grids: 7 indices at G = 16384).  The geometry kernels then stage their texels with TMA boxes whatever the sizes;
     // nullptr = identity, the DEM itself is that image.  The fragment stage always reads the DEM proper.
     float* d_hgrid = nullptr; float* d_hgrid_back = nullptr; uint32_t hpitch = 0;
+    // (min, max) of every 32 x 32 block of vertex heights of that image (k_hminmax): k_geom_march bounds a task's
+    // heights with it and skips the per-vertex clip tests where the task's box is provably inside the guard band
+    float2* d_hmm = nullptr; float2* d_hmm_back = nullptr; uint32_t hmm_nb = 0;
     bool use_tma = false;                // texels of the geometry pass are staged with TMA
     bool geom_tiled = false;             // VF_GEOM_TILED at creation: tiled k_geom instead of k_geom_march (A/B runs)
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
@@ -112,7 +115,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
     cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag); cudaFree(s->d_segtab);
-    cudaFree(s->d_dem_back); cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
+    cudaFree(s->d_dem_back); cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back); cudaFree(s->d_hmm); cudaFree(s->d_hmm_back);
     if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
     if (s->ev_front_released) cudaEventDestroy(s->ev_front_released);
@@ -206,6 +209,41 @@ k_resample(const VfAxis* __restrict__ axis, const float* __restrict__ dem, uint3
 }
 static void launch_resample(const vf_scene* s, const float* dem, float* hgrid, cudaStream_t st);
 
+// (min, max) of one 32 x 32 block of the G x G vertex-height image per CTA; a block holding a NaN or an infinity
+// gets (-inf, +inf), which no task passes
+__global__ void __launch_bounds__(256)
+k_hminmax(const float* __restrict__ img, uint32_t pitch, uint32_t G, uint32_t nb, float2* __restrict__ out) {
+    __shared__ float s_lo[8], s_hi[8];
+    const uint32_t bi = blockIdx.x, bj = blockIdx.y, tid = threadIdx.x;
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+    bool bad = false;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t i = bi * 32u + (tid & 31u), j = bj * 32u + (tid >> 5) + 8u * k;
+        if (i < G && j < G) {
+            const float v = __ldg(img + (size_t)j * pitch + i);
+            bad = bad || !isfinite(v);
+            lo = fminf(lo, v); hi = fmaxf(hi, v);
+        }
+    }
+    if (bad) { lo = __int_as_float(0xff800000); hi = __int_as_float(0x7f800000); }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+    }
+    if ((tid & 31u) == 0u) { s_lo[tid >> 5] = lo; s_hi[tid >> 5] = hi; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int k = 1; k < 8; ++k) { lo = fminf(lo, s_lo[k]); hi = fmaxf(hi, s_hi[k]); }
+        out[(size_t)bj * nb + bi] = make_float2(lo, hi);
+    }
+}
+// the image the geometry pass stages its texels from (vertex heights): the resampled one, else the DEM itself
+static void launch_hminmax(const vf_scene* s, const float* dem, const float* hgrid, float2* hmm, cudaStream_t st) {
+    k_hminmax<<<dim3(s->hmm_nb, s->hmm_nb), 256, 0, st>>>(hgrid ? hgrid : dem, hgrid ? s->hpitch : s->pitch, s->G, s->hmm_nb, hmm);
+}
+
 // every entry point works on the scene's own device, whatever vf_init selected since its creation
 static int scene_bind(const vf_scene* s) {
     if (!s) return vf_set_error(VF_E_INVALID, "null scene");
@@ -269,6 +307,19 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     } else {
         cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
         s->d_hgrid = s->d_hgrid_back = nullptr; s->hpitch = 0;
+    }
+    if (s->use_tma) {
+        const uint32_t nb = (s->G + 31u) / 32u;
+        if (!s->d_hmm || s->hmm_nb != nb) {
+            cudaFree(s->d_hmm); cudaFree(s->d_hmm_back);
+            s->d_hmm = s->d_hmm_back = nullptr; s->hmm_nb = nb;
+            VF_CUDA(cudaMalloc(&s->d_hmm, (size_t)nb * nb * sizeof(float2)));
+        }
+        launch_hminmax(s, s->d_dem, s->d_hgrid, s->d_hmm, s->stream);
+        VF_CUDA(cudaGetLastError());
+    } else {
+        cudaFree(s->d_hmm); cudaFree(s->d_hmm_back);
+        s->d_hmm = s->d_hmm_back = nullptr; s->hmm_nb = 0;
     }
     VF_CUDA(cudaStreamSynchronize(s->stream));
     return VF_OK;
@@ -497,8 +548,9 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         if (need > dbg_words) { if (d_dbg) cudaFree(d_dbg); VF_CUDA(cudaMalloc(&d_dbg, need * 8)); dbg_words = need; }
         VF_CUDA(cudaMemsetAsync(d_dbg, 0, need * 8, s->stream));
     }
+    static const bool no_safe = getenv("VF_GM_NO_SAFE") != nullptr;      // A/B: per-vertex clip tests in every task
 #define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
-        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, s->segtab_nfull, s->segtab_rows, dbg_path ? d_dbg : nullptr)
+        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, s->segtab_nfull, s->segtab_rows, (s->use_tma && !no_safe) ? s->d_hmm : nullptr, s->hmm_nb, dbg_path ? d_dbg : nullptr)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
     else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }
@@ -593,7 +645,7 @@ static int scene_apply_pending_dem(vf_scene* s) {
     VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_uploaded, 0));
     VF_CUDA(cudaEventRecord(s->ev_front_released, s->stream));   // every frame of the old image precedes this
     s->front_released_once = true;
-    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back);
+    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back); std::swap(s->d_hmm, s->d_hmm_back);
     std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
     s->back_pending = false;
     return VF_OK;
@@ -678,7 +730,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 
 // ---- pipelined interface: uploads and batches overlap across calls -------------------------------
 static void scene_swap_images(vf_scene* s) {
-    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back);
+    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back); std::swap(s->d_hmm, s->d_hmm_back); std::swap(s->d_hmm, s->d_hmm_back);
     std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
 }
 
@@ -736,6 +788,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
         VF_CUDA(cudaMalloc(&s->d_hgrid_back, (size_t)s->hpitch * s->G * 4));
         s->back_valid = false;
     }
+    if (s->d_hmm && !s->d_hmm_back) VF_CUDA(cudaMalloc(&s->d_hmm_back, (size_t)s->hmm_nb * s->hmm_nb * sizeof(float2)));
     if (!s->back_valid) {
         const bool ok = !s->use_tma || (s->d_hgrid ? scene_encode_maps(s->d_hgrid_back, s->G, s->G, s->hpitch, &s->dem_map_b, s->dem_map_gm_b)
                                                    : scene_encode_maps(s->d_dem_back, w, h, pitch, &s->dem_map_b, s->dem_map_gm_b));
@@ -749,6 +802,10 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
                               cudaMemcpyHostToDevice, s->upload_stream));
     if (s->d_hgrid_back) {                        // vertex heights of the new image, behind its upload
         launch_resample(s, s->d_dem_back, s->d_hgrid_back, s->upload_stream);
+        VF_CUDA(cudaGetLastError());
+    }
+    if (s->d_hmm_back) {
+        launch_hminmax(s, s->d_dem_back, s->d_hgrid_back, s->d_hmm_back, s->upload_stream);
         VF_CUDA(cudaGetLastError());
     }
     VF_CUDA(cudaEventRecord(s->ev_uploaded, s->upload_stream));

@@ -60,6 +60,20 @@ typedef struct {
     float ms_geom, ms_bin, ms_raster, ms_total; /* CUDA-event times, only when timing enabled */
 } vf_frame_stats_t;
 
+/* timing and traffic of a scene (planned in the reference as render_metrics(): ROADMAP.md:1959-1967) */
+typedef struct {
+    float upload_ms;     /* last height upload: H2D copy (+ vertex-height resample and bounds), CUDA events on its stream */
+    float gpu_ms;        /* kernels of the last render call, all its frames (CUDA events on the render stream) */
+    float readback_ms;   /* device-to-host copies of the last render call (CUDA events on the copy stream) */
+    float encode_ms;     /* PNG encoding of the last render_png / render_batch_png call (device deflate + host framing) */
+    float total_ms;      /* host wall clock of the last render call, submit to completion */
+    uint32_t frames;     /* frames of the last render call */
+    uint32_t reserved;
+    uint64_t last_h2d_bytes, last_d2h_bytes;   /* bytes of the last upload / the last render call */
+    uint64_t h2d_bytes, d2h_bytes;             /* cumulative since the scene was created */
+    uint64_t vram_bytes;                       /* device memory the scene currently holds */
+} vf_render_metrics_t;
+
 /* ---- context ----------------------------------------------------------------------
  * replaces: WgpuContext::get() src/lib.rs:31-60 and the per-object device creation in
  * src/terrain/mod.rs:277-294, src/scene/mod.rs:63-70 */
@@ -70,6 +84,10 @@ int vf_device_info(int device, vf_device_info_t *out);   /* src/lib.rs:744-845 d
 /* pinned host memory for zero-staging readback (numpy arrays are built on top of it) */
 int vf_host_alloc(size_t bytes, void **out);
 int vf_host_free(void *p);
+/* driver / runtime versions (as cudaDriverGetVersion reports them) and the flags libvfcuda.so was compiled with
+ * (vulkan_forge.report_environment(), planned in the reference: ROADMAP.md:1989-1999) */
+int vf_versions(int *driver, int *runtime);
+const char *vf_build_info(void);
 
 /* ---- triangle path ------------------------------------------------------------------
  * replaces: render_into_offscreen + copy_texture_to_rgba_unpadded, src/lib.rs:162-216,685-721,
@@ -94,6 +112,17 @@ int vf_dem_normalize(float *data, size_t n, int mode, float eps, float lo, float
 int vf_dem_ingest_f64(const double *src, size_t n, float scale, float *dst);
 int vf_dem_ingest_f32(const float *src, size_t n, float scale, float *dst);
 
+/* ---- device-resident height images ----------------------------------------------------------
+ * replaces: the Vec<f32> that Renderer.add_terrain keeps on the host (src/lib.rs:351-418) and everything computed
+ * from it (terrain_stats :424-429, normalize_terrain :478-493, upload_height_r32f :496-571).  The array crosses
+ * the bus once (cast / scaled on the device); statistics, normalisation and scenes then work on the device copy. */
+int vf_height_ingest_f32(const float *host, uint32_t w, uint32_t h, float scale, vf_height **out);
+int vf_height_ingest_f64(const double *host, uint32_t w, uint32_t h, float scale, vf_height **out);
+int vf_height_clone(const vf_height *src, vf_height **out);
+int vf_height_minmax(const vf_height *t, int clamp, float *lo, float *hi);
+int vf_height_stats(const vf_height *t, float out4[4]);              /* min,max,mean,std */
+int vf_height_normalize(vf_height *t, int mode, float eps, float lo, float hi);
+
 /* ---- R32F height image round trip -----------------------------------------------------
  * replaces: Renderer.upload_height_r32f / debug_read_height_patch / read_full_height_texture,
  * src/lib.rs:496-681 (256-byte row padding is an artefact of wgpu and is gone). */
@@ -115,6 +144,8 @@ int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_unorm, vf_s
 void vf_scene_destroy(vf_scene *s);
 /* src/scene/mod.rs:227-276: copies the host array into a device image (pitch multiple of 16 B) */
 int vf_scene_set_height_f32(vf_scene *s, const float *host, uint32_t w, uint32_t h);
+/* the same from a device-resident image: a device-to-device copy, no PCIe crossing */
+int vf_scene_set_height_image(vf_scene *s, const vf_height *t);
 /* TerrainUniforms as 44 f32, src/terrain/mod.rs:114-142 (view, proj column-major, ...) */
 int vf_scene_set_uniforms(vf_scene *s, const float u44[44]);
 int vf_scene_get_uniforms(const vf_scene *s, float u44[44]);
@@ -135,18 +166,27 @@ int vf_scene_render_batch(vf_scene *s, const float *u44xn, int n, uint8_t *out_r
 int vf_scene_set_height_f32_async(vf_scene *s, const float *host_pinned, uint32_t w, uint32_t h);
 int vf_scene_render_batch_async(vf_scene *s, const float *u44xn, int n, uint8_t *out_rgba_host_pinned, int *ticket);
 int vf_scene_wait(vf_scene *s, int ticket);
+/* n frames rendered AND PNG-encoded on the device (Sub filter + fixed-Huffman deflate with one-pixel matches, one IDAT
+ * chunk per band of rows, CRC-32 and Adler-32 computed on the device): only the finished files cross the bus.  File k
+ * occupies out_host[k * cap_per_file ...] for sizes[k] bytes; size the slots with vf_png_file_bound (worst case, about
+ * 1.13 x the raw frame).  replaces: render + readback + image::save, src/scene/mod.rs:279-335, for batches. */
+size_t vf_png_file_bound(int w, int h);
+int vf_scene_render_batch_png(vf_scene *s, const float *u44xn, int n, uint8_t *out_host, size_t cap_per_file, uint32_t *sizes);
 /* n frames left in device memory (no D2H); for kernel-only timing */
 int vf_scene_render_device(vf_scene *s, const float *u44xn, int n);
 /* visibility of the last frame: per pixel 0 = clear colour, else primitive id + 1 */
 int vf_scene_debug_visibility(vf_scene *s, uint32_t *out_host);
 int vf_scene_enable_timing(vf_scene *s, int enabled);
 int vf_scene_last_stats(const vf_scene *s, vf_frame_stats_t *out);
+int vf_scene_metrics(const vf_scene *s, vf_render_metrics_t *out);
 /* run on a caller-owned cudaStream_t (e.g. torch's current stream); NULL = private stream */
 int vf_scene_set_stream(vf_scene *s, void *cuda_stream);
 
 /* ---- PNG ------------------------------------------------------------------------------
  * replaces: image::RgbaImage::save, src/scene/mod.rs:331-333 (RGBA8, zlib deflate) */
 int vf_png_write(const char *path, const uint8_t *rgba, int w, int h);
+/* any host RGBA8 image through the device encoder of vf_scene_render_batch_png: the finished file's bytes in out_host */
+int vf_png_encode_rgba(const uint8_t *rgba_host, int w, int h, uint8_t *out_host, size_t cap, uint32_t *size);
 
 #ifdef __cplusplus
 }

@@ -51,6 +51,27 @@ def test_c4_orbit_shards_equal_whole(ext, vf, dem4096):
     assert len({hashlib.sha256(f.tobytes()).hexdigest() for f in whole}) == 8    # every camera differs
 
 
+@pytest.mark.parametrize("depth", [False, True], ids=["no depth", "depth"])
+def test_c4_orbit_vs_oracle(ext, vf, oracle, luts, dem4096, depth):
+    """config 4: frames k = 0, 341, 683 of the 1024-frame orbit at 1024 x 1024 over the 4096^2 DEM (G = 4096),
+    NORTHSTAR, byte-compared with the oracle (the config the multi-GPU split is defined on)."""
+    sc = ext.Scene(1024, 1024, grid=4096, colormap="terrain")
+    sc.set_height_from_r32f(dem4096)
+    sc.set_shading("northstar", depth=depth)
+    sc.set_sun(35.0, 120.0)
+    sc.set_exposure(1.1)
+    lo, hi = sc.set_auto_height_range()
+    cams = vf.orbit_cameras(1024)
+    ks = (0, 341, 683)
+    blocks = sc.camera_blocks([cams[k] for k in ks])
+    got = sc.render_batch_rgba(blocks)
+    for n, k in enumerate(ks):
+        ref = oracle.render_terrain(1024, 1024, 4096, dem4096, blocks[n], luts["terrain"], mode=oracle.MODE_NORTHSTAR, depth=depth,
+                                    h_min=float(lo), h_max=float(hi))
+        assert (ref[..., :3] != ref[0, 0, :3]).any(-1).mean() > 0.05, "camera sees nothing"
+        assert np.array_equal(got[n], ref), f"frame {k}: {(got[n] != ref).any(-1).sum()} pixels differ"
+
+
 def test_c5_4k_dem16384_depth(ext, oracle, luts, synthetic_dem):
     """config 5: 3840x2160, 16384^2 DEM, depth, magma, exaggeration 2, auto 1-99 %.  The oracle needs a
     few seconds per frame on many cores; compared in full."""

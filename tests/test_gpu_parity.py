@@ -71,6 +71,27 @@ def test_dem_minmax_bit_exact(ext, oracle, n):
         assert np.float32(lo).tobytes() == olo.tobytes() and np.float32(hi).tobytes() == ohi.tobytes()
 
 
+def test_dem_host_arrays_stream_in_chunks(ext, vf, oracle):
+    """Host arrays larger than one 64 MiB chunk: min / max / statistics accumulate across chunks, the sign of a zero
+    extreme is that of the first zero of the whole array, and the percentile call moves 256 KB, not the array."""
+    import time
+    n = (16 << 20) * 2 + 12345
+    rng = np.random.default_rng(5)
+    a = np.abs(rng.normal(size=n)).astype(np.float32) + np.float32(0.5)
+    a[(16 << 20) + 7] = -0.0                      # first zero sits in the second chunk: min must be -0.0
+    a[(16 << 20) * 2 + 99] = 0.0
+    lo, hi = ext.dem_minmax(a, False)
+    olo, ohi = oracle.min_max(a, False)
+    assert np.float32(lo).tobytes() == olo.tobytes() and np.float32(hi).tobytes() == ohi.tobytes() and np.signbit(np.float32(lo))
+    assert ext.dem_minmax(a, True) == tuple(float(x) for x in oracle.min_max(a, True))
+    ext.dem_minmax(a, True)
+    t0 = time.perf_counter()
+    for _ in range(5):
+        ext.dem_minmax(a, True)
+    per_call_ms = (time.perf_counter() - t0) / 5 * 1e3
+    assert per_call_ms < 3.0, f"percentile of a host array took {per_call_ms:.2f} ms: the whole array is being uploaded again?"
+
+
 def test_dem_percentile_ties_zeros_and_outliers(ext, oracle):
     rng = np.random.default_rng(0)
     a = np.round(rng.normal(size=200_000), 1).astype(np.float32)       # heavy ties

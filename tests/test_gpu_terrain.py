@@ -326,6 +326,7 @@ def test_renderer_draws_stored_terrain(vf, oracle, luts, synthetic_dem):
     r.add_terrain(dem, (1.0, 1.0), 2.0, "terrain")
     r.set_sun(35.0, 120.0)
     r.set_exposure(1.1)
+    r.set_camera_look_at((3.0, 2.0, 3.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 45.0, 0.1, 100.0)
     a = r.render_rgba()
     hmin, hmax = oracle.h_range(dem * np.float32(2.0))
     u = oracle.look_at_uniforms(240, 160, (3, 2, 3), sun=oracle.sun_dir(35.0, 120.0), exposure=1.1,
@@ -335,6 +336,88 @@ def test_renderer_draws_stored_terrain(vf, oracle, luts, synthetic_dem):
     assert np.array_equal(a, ref)
     r.set_sun(35.0, 300.0)                                             # flipping the sun changes the shading
     assert not np.array_equal(a, r.render_rgba())
+
+
+def test_renderer_framing_camera_spacing_and_device_resident_terrain(vf, oracle, luts):
+    """Until set_camera_look_at is called the Renderer frames the terrain from the south (north = +X up, east = +Z to
+    the right); spacing scales the plane (terrain.wgsl:58); float64 input, statistics and normalisation run on the
+    device copy made by add_terrain and the frame equals the oracle's on that copy."""
+    yy, xx = np.mgrid[0:96, 0:96]
+    dem = (40.0 * np.exp(-(((xx - 47.5) ** 2 + (yy - 47.5) ** 2) / 96.0 ** 2) / (2 * 0.18 ** 2))).astype(np.float64)
+    r = vf.Renderer(160, 120)
+    r.add_terrain(dem, (30.0, 30.0), 1.0, "viridis")
+    h32 = dem.astype(np.float32)
+    lo, hi = r.height_range()
+    olo, ohi = oracle.h_range(h32)
+    assert (np.float32(lo), np.float32(hi)) == (olo, ohi)
+    mn, mx, mean, std = r.terrain_stats()
+    assert mn == h32.min() and mx == h32.max() and abs(mean - h32.mean()) < 1e-3 * abs(h32.mean()) and abs(std - h32.std()) < 1e-3 * h32.std()
+    r.set_sun(45.0, 90.0)                                              # sun in the east
+    east = r.render_rgba()
+    R = max(45.0 * np.float32(1.41421356), 0.5 * (hi - lo))
+    hmid = np.float32(0.5) * (np.float32(lo) + np.float32(hi))
+    eye = (float(np.float32(-1.5) * np.float32(R)), float(hmid + np.float32(1.0) * np.float32(R)), 0.0)
+    u = oracle.look_at_uniforms(160, 120, eye, (0.0, float(hmid), 0.0), (0, 1, 0), 45.0, float(np.float32(0.05) * np.float32(R)),
+                                float(np.float32(12.0) * np.float32(R)), sun=oracle.sun_dir(45.0, 90.0), spacing=30.0,
+                                h_min=float(lo), h_max=float(hi), normalize_sun=False)
+    ref = oracle.render_terrain(160, 120, 96, h32, u, luts["viridis"], mode=oracle.MODE_NORTHSTAR, depth=True, h_min=float(lo), h_max=float(hi))
+    assert np.array_equal(east, ref), f"{(east != ref).any(-1).sum()} pixels differ"
+    r.set_sun(45.0, 270.0)
+    west = r.render_rgba()
+    lum = lambda im: im[..., :3].astype(np.float32) @ np.float32([0.2126, 0.7152, 0.0722])   # noqa: E731
+    y, cx = 60, 80                 # east sun: the east flank (right of the summit) is brighter than under a west sun, and vice versa
+    assert lum(east)[y, cx + 14] > lum(west)[y, cx + 14] and lum(west)[y, cx - 14] > lum(east)[y, cx - 14]
+    r.normalize_terrain("minmax", (0.0, 1.0))                          # in place on the device copy; next frame sees it
+    mn, mx, _, _ = r.terrain_stats()
+    assert abs(mn) < 1e-6 and abs(mx - 1.0) < 1e-6
+    assert not np.array_equal(west, r.render_rgba())
+    m = r.render_metrics()
+    assert m["d2h_bytes"] == 160 * 120 * 4 and m["vram_bytes"] > 0 and m["gpu_ms"] > 0
+
+
+def test_render_metrics_and_report_environment(ext, vf, synthetic_dem):
+    """render_metrics(): ROADMAP.md:1959-1967 (encode_ms, gpu_ms, readback_ms, total_ms, vram_bytes) plus byte counts;
+    report_environment(): ROADMAP.md:1989-1999."""
+    W, H, G = 320, 200, 256
+    dem = synthetic_dem(3, G)
+    sc = ext.Scene(W, H, grid=G, colormap="viridis")
+    sc.set_height_from_r32f(dem)
+    n = 5
+    frames = sc.render_batch_rgba(vf.orbit_cameras(16)[:n])
+    m = sc.render_metrics()
+    for k in ("upload_ms", "gpu_ms", "readback_ms", "encode_ms", "total_ms", "h2d_bytes", "d2h_bytes", "vram_bytes", "frames"):
+        assert k in m, k
+    assert m["d2h_bytes"] == W * H * 4 * n == frames.nbytes and m["frames"] == n
+    assert m["h2d_bytes"] == dem.nbytes and m["upload_ms"] > 0 and m["gpu_ms"] > 0 and m["readback_ms"] > 0
+    assert m["total_ms"] >= m["gpu_ms"] * 0.5 and m["vram_bytes"] >= dem.nbytes + 2 * W * H * 4 + W * H * 8
+    sc.render_batch_device(vf.orbit_cameras(16)[:2])
+    m = sc.render_metrics()
+    assert m["d2h_bytes"] == 0 and m["frames"] == 2 and m["readback_ms"] == 0
+    tk = sc.render_batch_rgba_async(vf.orbit_cameras(16)[:3])
+    sc.collect(tk)
+    assert sc.render_metrics()["d2h_bytes"] == W * H * 4 * 3
+    env = vf.report_environment()
+    for k in ("os", "python", "package_version", "backend", "adapters", "cuda_driver_version", "cuda_runtime_version", "build"):
+        assert k in env, k
+    assert env["adapters"] and "B200" in env["adapters"][0]["name"] or env["adapters"][0]["backend"] == "CUDA"
+    assert "sm_100a" in env["build"] and env["cuda_driver_version"]
+
+
+def test_device_render_between_async_batch_and_collect(ext, vf, synthetic_dem):
+    """A device-only render issued while an async batch still drains its frame slots to the host must not tear that
+    batch (the slots wait for their copies whatever the later call does with its frames)."""
+    W, H, G = 512, 384, 512
+    sc = ext.Scene(W, H, grid=G, colormap="terrain")
+    sc.set_height_from_r32f(synthetic_dem(6, G))
+    sc.set_shading("northstar", depth=True)
+    sc.set_auto_height_range()
+    cams = vf.orbit_cameras(24)
+    want = np.array(sc.render_batch_rgba(cams[:8]))
+    for _ in range(3):
+        tk = sc.render_batch_rgba_async(cams[:8])
+        sc.render_batch_device(cams[8:16])
+        sc.debug_visibility()
+        assert np.array_equal(sc.collect(tk), want)
 
 
 def test_tma_staging_matches_gather_path(ext, synthetic_dem, monkeypatch):
@@ -385,3 +468,81 @@ def test_pipelined_batches_equal_synchronous(ext, vf, synthetic_dem):
         sc.collect(0)
     # the synchronous path still works afterwards and sees the last uploaded image
     assert np.array_equal(sc.render_batch_rgba(cams), want[1])
+
+
+# ---- PNG encoded on the device ----------------------------------------------------------------
+def _png_chunks(data):
+    import struct
+    import zlib
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, out = 8, []
+    while pos < len(data):
+        n, typ = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        crc, = struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])
+        assert crc == (zlib.crc32(typ + body) & 0xffffffff), f"bad CRC in {typ} chunk at {pos}"
+        out.append((typ, body))
+        pos += 12 + n
+    assert pos == len(data) and out[0][0] == b"IHDR" and out[-1] == (b"IEND", b"")
+    return out
+
+
+def _png_decode(data, w, h):
+    """Independent decoder: chunk CRCs, zlib (checks the Adler-32), Sub / None filters -> (h, w, 4) uint8."""
+    import zlib
+    chunks = _png_chunks(data)
+    raw = np.frombuffer(zlib.decompress(b"".join(b for t, b in chunks if t == b"IDAT")), np.uint8).reshape(h, 4 * w + 1)
+    assert set(np.unique(raw[:, 0])) <= {0, 1}
+    px = raw[:, 1:].reshape(h, w, 4).astype(np.uint32)
+    sub = raw[:, 0] == 1
+    px[sub] = np.cumsum(px[sub], axis=1) & 255
+    return px.astype(np.uint8)
+
+
+@pytest.mark.parametrize("size", [(1, 1), (7, 3), (64, 64), (333, 77), (1920, 1080), (8192, 3)])
+def test_device_png_encoder_arbitrary_images(ext, size):
+    """Noise (every byte a literal: the 9-bits-per-byte worst case), flat colour (one long run), a gradient and
+    period-4 patterns survive the device encoder byte for byte; PIL reads the files too."""
+    from PIL import Image
+    import io
+    w, h = size
+    rng = np.random.default_rng(w * 131 + h)
+    yy, xx = np.mgrid[0:h, 0:w]
+    images = {
+        "noise": rng.integers(0, 256, (h, w, 4), dtype=np.uint8),
+        "flat": np.full((h, w, 4), (39, 39, 48, 255), np.uint8),
+        "gradient": np.stack([xx & 255, yy & 255, (xx + yy) & 255, np.full_like(xx, 255)], -1).astype(np.uint8),
+        "mixed": np.where((xx // 37 + yy // 11)[..., None] % 2 == 0, rng.integers(0, 256, (h, w, 4)), 200).astype(np.uint8),
+    }
+    for name, img in images.items():
+        data = ext.png_encode_device(img)
+        assert np.array_equal(_png_decode(data, w, h), img), name
+        assert np.array_equal(np.asarray(Image.open(io.BytesIO(data)).convert("RGBA")), img), name
+    assert len(ext.png_encode_device(images["flat"])) < 0.02 * w * h * 4 + 600      # runs collapse to 13 bits per 258 bytes
+
+
+def test_device_png_batch_equals_rgba_frames(ext, vf, synthetic_dem, tmp_path):
+    """Scene.render_batch_png / render_batch_png_bytes / render_png: every file decodes to the bytes render_batch_rgba
+    returns for the same camera; only the compressed bytes cross the bus (render_metrics)."""
+    from PIL import Image
+    W, H, G = 640, 360, 512
+    sc = ext.Scene(W, H, grid=G, colormap="terrain")
+    sc.set_height_from_r32f(synthetic_dem(7, G))
+    sc.set_shading("northstar", depth=True)
+    sc.set_auto_height_range()
+    cams = vf.orbit_cameras(16)[:7]
+    want = np.array(sc.render_batch_rgba(cams))
+    blobs = sc.render_batch_png_bytes(cams)
+    m = sc.render_metrics()
+    assert m["d2h_bytes"] == sum(len(b) for b in blobs) < 0.5 * want.nbytes
+    for k, b in enumerate(blobs):
+        assert np.array_equal(_png_decode(b, W, H), want[k]), k
+    paths = [str(tmp_path / f"f{k}.png") for k in range(len(cams))]
+    sc.render_batch_png(paths, cams)
+    for k, p in enumerate(paths):
+        assert np.array_equal(np.asarray(Image.open(p).convert("RGBA")), want[k]), k
+    sc.set_camera_look_at(*cams[3])
+    sc.render_png(str(tmp_path / "one.png"))
+    assert np.array_equal(np.asarray(Image.open(tmp_path / "one.png").convert("RGBA")), want[3])
+    with pytest.raises(ValueError):
+        sc.render_batch_png(paths[:2], cams)

@@ -9,5 +9,5 @@ OUT=$ROOT/build/variants/$NAME
 mkdir -p $OUT
 C=$ROOT/vulkan-forge_b200/csrc
 /usr/local/cuda/bin/nvcc $@ -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 --fmad=false -std=c++17 -ccbin /usr/bin/g++ \
-  -Xcompiler -fPIC,-ffp-contract=off -shared -o $OUT/libvfcuda.so $C/vf_context.cu $C/vf_terrain.cu $C/vf_dem.cu $C/vf_misc.cu $C/vf_png.cpp -lz
+  -Xcompiler -fPIC,-ffp-contract=off -shared -o $OUT/libvfcuda.so $C/vf_context.cu $C/vf_terrain.cu $C/vf_dem.cu $C/vf_misc.cu $C/vf_png_dev.cu $C/vf_png.cpp -lz
 echo built $OUT/libvfcuda.so

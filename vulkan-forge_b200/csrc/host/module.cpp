@@ -9,9 +9,11 @@
 
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -178,6 +180,7 @@ public:
     py::array_t<uint8_t> render_rgba() {
         auto out = pinned_array<uint8_t>({(py::ssize_t)height_, (py::ssize_t)width_, 4});
         uint8_t* p = out.mutable_data();
+        encode_ms_ = 0.0f;
         {
             py::gil_scoped_release nogil;
             check(vf_scene_render_rgba(scene_, p));
@@ -185,11 +188,39 @@ public:
         return out;
     }
 
+    // The frame is encoded on the device (vf_png_dev.cu) and only the file's bytes come back: src/scene/mod.rs:279-335
+    // without the raw readback.  VF_PNG_HOST=1 keeps the round-1 path (raw readback + zlib on host threads).
     void render_png(const std::string& path) {
-        auto img = render_rgba();
-        const uint8_t* p = img.data();
-        py::gil_scoped_release nogil;
-        check(vf_png_write(path.c_str(), p, (int)width_, (int)height_));
+        if (std::getenv("VF_PNG_HOST")) {
+            auto img = render_rgba();
+            const uint8_t* p = img.data();
+            py::gil_scoped_release nogil;
+            const auto t0 = std::chrono::steady_clock::now();
+            check(vf_png_write(path.c_str(), p, (int)width_, (int)height_));
+            encode_ms_ = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+            return;
+        }
+        float u[44];
+        check(vf_scene_get_uniforms(scene_, u));
+        std::vector<std::string> paths{path};
+        png_batch(u, 1, &paths, nullptr);
+    }
+    // n frames -> n .png files; cameras as for render_batch_rgba
+    void render_batch_png(const std::vector<std::string>& paths, py::object cameras) {
+        const std::vector<float> blocks = camera_blocks(cameras);
+        const int n = (int)(blocks.size() / 44);
+        if (n == 0) throw py::value_error("no cameras given");
+        if ((size_t)n != paths.size()) throw py::value_error("need one path per camera");
+        png_batch(blocks.data(), n, &paths, nullptr);
+    }
+    // n frames -> list of bytes objects (each a complete .png file)
+    py::list render_batch_png_bytes(py::object cameras) {
+        const std::vector<float> blocks = camera_blocks(cameras);
+        const int n = (int)(blocks.size() / 44);
+        if (n == 0) throw py::value_error("no cameras given");
+        py::list out;
+        png_batch(blocks.data(), n, nullptr, &out);
+        return out;
     }
 
     py::array_t<float> debug_uniforms_f32() const {
@@ -337,10 +368,19 @@ public:
     }
     void enable_timing(bool on) { check(vf_scene_enable_timing(scene_, on ? 1 : 0)); }
     void set_stream(uintptr_t cuda_stream) { check(vf_scene_set_stream(scene_, reinterpret_cast<void*>(cuda_stream))); }
+    void set_height_image(const vf_height* img) { check(vf_scene_set_height_image(scene_, img)); }
+    // kernel statistics of the last frame plus the timing / traffic block the reference planned as render_metrics()
+    // (ROADMAP.md:1959-1967: encode_ms, gpu_ms, readback_ms, total_ms, vram_bytes)
     py::dict render_metrics() const {
         vf_frame_stats_t st;
         check(vf_scene_last_stats(scene_, &st));
+        vf_render_metrics_t rm;
+        check(vf_scene_metrics(scene_, &rm));
         py::dict d;
+        d["upload_ms"] = rm.upload_ms; d["gpu_ms"] = rm.gpu_ms; d["readback_ms"] = rm.readback_ms; d["encode_ms"] = encode_ms_;
+        d["total_ms"] = rm.total_ms + encode_ms_; d["frames"] = rm.frames;
+        d["h2d_bytes"] = rm.last_h2d_bytes; d["d2h_bytes"] = rm.last_d2h_bytes;
+        d["h2d_bytes_total"] = rm.h2d_bytes; d["d2h_bytes_total"] = rm.d2h_bytes; d["vram_bytes"] = rm.vram_bytes;
         d["bin_pairs"] = st.bin_pairs; d["bin_capacity"] = st.bin_capacity;
         d["clipped_prims"] = st.clipped_prims; d["tiles"] = st.tiles; d["big_prims"] = st.big_prims; d["tma"] = st.tma;
         d["ms_geom"] = st.ms_geom; d["ms_bin"] = st.ms_bin; d["ms_raster"] = st.ms_raster; d["ms_total"] = st.ms_total;
@@ -351,6 +391,31 @@ public:
     uint32_t grid() const { return grid_; }
 
 private:
+    // render + encode on the device, files into pinned host memory, then to disk and / or bytes objects
+    void png_batch(const float* blocks, int n, const std::vector<std::string>* paths, py::list* bytes_out) {
+        const size_t cap = (vf_png_file_bound((int)width_, (int)height_) + 255) & ~(size_t)255;
+        auto buf = pinned_array<uint8_t>({(py::ssize_t)n, (py::ssize_t)cap});
+        std::vector<uint32_t> sizes((size_t)n);
+        uint8_t* p = buf.mutable_data();
+        std::string io_error;
+        {
+            py::gil_scoped_release nogil;
+            check(vf_scene_render_batch_png(scene_, blocks, n, p, cap, sizes.data()));
+            const auto t0 = std::chrono::steady_clock::now();
+            if (paths) {
+                for (int k = 0; k < n && io_error.empty(); ++k) {
+                    FILE* f = std::fopen((*paths)[k].c_str(), "wb");
+                    if (!f) { io_error = "cannot open '" + (*paths)[k] + "' for writing"; break; }
+                    const bool ok = std::fwrite(p + (size_t)k * cap, 1, sizes[k], f) == sizes[k];
+                    if (std::fclose(f) != 0 || !ok) io_error = "short write to '" + (*paths)[k] + "'";
+                }
+            }
+            encode_ms_ = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();   // host share: file output
+        }
+        if (!io_error.empty()) throw std::runtime_error(io_error);
+        if (bytes_out)
+            for (int k = 0; k < n; ++k) bytes_out->append(py::bytes(reinterpret_cast<const char*>(p + (size_t)k * cap), sizes[k]));
+    }
     void push_uniforms() {
         float u[44];
         globals_.to_uniforms(view_, proj_, u);
@@ -367,6 +432,7 @@ private:
     M4 view_, proj_;
     int mode_ = VF_MODE_SHIPPED;
     bool depth_ = false;
+    float encode_ms_ = 0.0f;
 };
 
 struct Scene : TerrainObject {

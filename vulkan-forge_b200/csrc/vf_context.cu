@@ -142,6 +142,22 @@ extern "C" int vf_device_info(int device, vf_device_info_t* out) {
     return VF_OK;
 }
 
+extern "C" int vf_versions(int* driver, int* runtime) {
+    int d = 0, r = 0;
+    if (cudaDriverGetVersion(&d) != cudaSuccess) { (void)cudaGetLastError(); d = 0; }
+    if (cudaRuntimeGetVersion(&r) != cudaSuccess) { (void)cudaGetLastError(); r = 0; }
+    if (driver) *driver = d;
+    if (runtime) *runtime = r;
+    return VF_OK;
+}
+
+#define VF_STR2(x) #x
+#define VF_STR(x) VF_STR2(x)
+extern "C" const char* vf_build_info(void) {
+    return "libvfcuda: nvcc " VF_STR(__CUDACC_VER_MAJOR__) "." VF_STR(__CUDACC_VER_MINOR__) "." VF_STR(__CUDACC_VER_BUILD__)
+           ", -gencode arch=compute_100a,code=sm_100a -O3 --fmad=false -lineinfo, built " __DATE__;
+}
+
 extern "C" int vf_host_alloc(size_t bytes, void** out) {
     int rc = vf_require_device();
     if (rc) return rc;
@@ -159,6 +175,61 @@ extern "C" int vf_host_free(void* p) {
     if (!p) return VF_OK;
     VF_CUDA(cudaFreeHost(p));
     return VF_OK;
+}
+
+// ---- utility stream + scratch, per device ------------------------------------------------
+static std::mutex g_util_mu;
+static cudaStream_t g_util_stream[kMaxDevices] = {nullptr};
+static void* g_scratch[kMaxDevices] = {nullptr};
+static size_t g_scratch_bytes[kMaxDevices] = {0};
+static void* g_pinned = nullptr;
+static size_t g_pinned_bytes = 0;
+
+std::mutex& vf_util_mutex() { return g_util_mu; }
+
+static int current_device() {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) { (void)cudaGetLastError(); return -1; }
+    return dev;
+}
+
+cudaStream_t vf_util_stream() {
+    const int dev = current_device();
+    if (dev < 0) { vf_set_error(VF_E_CUDA, "no current CUDA device"); return nullptr; }
+    if (!g_util_stream[dev] && cudaStreamCreateWithFlags(&g_util_stream[dev], cudaStreamNonBlocking) != cudaSuccess) {
+        vf_set_error(VF_E_CUDA, "utility stream: %s", cudaGetErrorString(cudaGetLastError()));
+        g_util_stream[dev] = nullptr;
+    }
+    return g_util_stream[dev];
+}
+
+void* vf_scratch(size_t bytes) {
+    const int dev = current_device();
+    if (dev < 0) { vf_set_error(VF_E_CUDA, "no current CUDA device"); return nullptr; }
+    if (bytes > g_scratch_bytes[dev]) {
+        if (g_scratch[dev]) { cudaStreamSynchronize(g_util_stream[dev]); cudaFree(g_scratch[dev]); g_scratch[dev] = nullptr; g_scratch_bytes[dev] = 0; }
+        const size_t want = (bytes + (1u << 20) - 1) & ~(size_t)((1u << 20) - 1);
+        if (cudaMalloc(&g_scratch[dev], want) != cudaSuccess) {
+            (void)cudaGetLastError();
+            vf_set_error(VF_E_OOM, "scratch allocation of %zu bytes failed", want);
+            return nullptr;
+        }
+        g_scratch_bytes[dev] = want;
+    }
+    return g_scratch[dev];
+}
+
+void* vf_pinned_scratch(size_t bytes) {
+    if (bytes > g_pinned_bytes) {
+        if (g_pinned) { cudaFreeHost(g_pinned); g_pinned = nullptr; g_pinned_bytes = 0; }
+        if (cudaHostAlloc(&g_pinned, bytes, cudaHostAllocDefault) != cudaSuccess) {
+            (void)cudaGetLastError();
+            vf_set_error(VF_E_OOM, "pinned staging allocation of %zu bytes failed", bytes);
+            return nullptr;
+        }
+        g_pinned_bytes = bytes;
+    }
+    return g_pinned;
 }
 
 // ---- palettes (bytes generated by tools/gen_lut_assets.py) -----------------------------

@@ -4,10 +4,14 @@
 // (src/lib.rs:351-388).
 //   k_dem_gather : strided sample (or all values) -> compact buffer        (HBM: 32-B sectors)
 //   k_dem_select : exact k-th order statistics by 4-pass 8-bit radix select (one CTA, L2/smem)
-//   k_dem_reduce : min / max / sum, then sum of squared deviations          (HBM streaming)
-//   k_dem_normalize, k_dem_ingest_* : elementwise                           (HBM streaming)
+//   k_dem_moments: min / max / shifted sums / first zero in ONE pass        (HBM streaming)
+//   k_dem_normalize, k_dem_ingest_f64, k_dem_scale : elementwise            (HBM streaming)
+// Host arrays stream through a cached per-device scratch allocation on a utility stream (no cudaMalloc per call);
+// device-resident images (vf_height) are processed in place.
 #include <math.h>
 #include <string.h>
+
+#include <thread>
 
 #include "vf_internal.h"
 
@@ -95,263 +99,435 @@ k_dem_select(const float* __restrict__ vals, uint32_t m, uint32_t rank0, uint32_
     }
 }
 
-// acc[0] = min key, acc[1] = max key (uint32), accd[0] = sum, accd[1] = sum (v-mean)^2
+// One pass over an image (or a chunk of a flat host array uploaded piecewise; `base` = index of its first element):
+//   acc[0] = min key, acc[1] = max key (order-preserving uint32 keys; NaN skipped as `if v < lo` skips it),
+//   accd[0] = sum (v - pivot), accd[1] = sum (v - pivot)^2 in double (mean and population variance follow; the shift
+//   by a pivot value keeps the single pass free of cancellation),
+//   first = index of the first +-0 of the slice.  `if v < lo { lo = v }` (terrain_stats.rs:17, lib.rs:914) keeps the
+//   FIRST element that equals the extreme value, and -0 == +0: when an extreme is zero its sign is that of the first
+//   zero in index order, which an order-free reduction cannot know.
 __global__ void __launch_bounds__(256)
-k_dem_reduce(const float* __restrict__ data, uint32_t w, uint32_t h, uint32_t pitch, int phase,
-             double mean, uint32_t* __restrict__ acc, double* __restrict__ accd) {
+k_dem_moments(const float* __restrict__ data, uint32_t w, uint32_t h, uint32_t pitch, unsigned long long base, float pivot,
+              uint32_t* __restrict__ acc, double* __restrict__ accd, unsigned long long* __restrict__ first) {
     __shared__ uint32_t s_mn[8], s_mx[8];
-    __shared__ double s_sum[8];
+    __shared__ double s_sum[8], s_sq[8];
     const size_t n = (size_t)w * h;
     uint32_t mn = 0xffffffffu, mx = 0u;
-    double sum = 0.0;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n;
-         idx += (size_t)gridDim.x * blockDim.x) {
+    double sum = 0.0, sq = 0.0;
+    unsigned long long zero_at = ~0ull;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
         const size_t r = idx / w, c = idx - r * w;
         const float v = __ldg(data + r * pitch + c);
-        if (phase == 0) {
-            if (v == v) { const uint32_t k = vf_float_key(v); mn = min(mn, k); mx = max(mx, k); }
-            sum += (double)v;
-        } else {
-            const double d = (double)v - mean;
-            sum += d * d;
-        }
+        if (v == v) { const uint32_t k = vf_float_key(v); mn = min(mn, k); mx = max(mx, k); }
+        if (v == 0.0f && zero_at == ~0ull) zero_at = base + idx;          // a thread's indices ascend
+        const double d = (double)v - (double)pivot;
+        sum += d; sq += d * d;
     }
+    if (zero_at != ~0ull) atomicMin(first, zero_at);
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, d));
         mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, d));
         sum += __shfl_xor_sync(0xffffffffu, sum, d);
+        sq += __shfl_xor_sync(0xffffffffu, sq, d);
     }
     const uint32_t lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
-    if (lane == 0) { s_mn[wid] = mn; s_mx[wid] = mx; s_sum[wid] = sum; }
+    if (lane == 0) { s_mn[wid] = mn; s_mx[wid] = mx; s_sum[wid] = sum; s_sq[wid] = sq; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int k = 1; k < 8; ++k) { mn = min(mn, s_mn[k]); mx = max(mx, s_mx[k]); sum += s_sum[k]; }
-        if (phase == 0) { atomicMin(&acc[0], mn); atomicMax(&acc[1], mx); atomicAdd(&accd[0], sum); }
-        else atomicAdd(&accd[1], sum);
+        for (int k = 1; k < 8; ++k) { mn = min(mn, s_mn[k]); mx = max(mx, s_mx[k]); sum += s_sum[k]; sq += s_sq[k]; }
+        atomicMin(&acc[0], mn); atomicMax(&acc[1], mx); atomicAdd(&accd[0], sum); atomicAdd(&accd[1], sq);
     }
 }
 
-// index of the first +-0 of the image.  `if v < lo { lo = v }` (terrain_stats.rs:17, lib.rs:914) keeps
-// the FIRST element that equals the extreme value, and -0 == +0: when an extreme is zero its sign is
-// the sign of the first zero in index order, which an order-free reduction cannot know.
-__global__ void __launch_bounds__(256)
-k_dem_first_zero(const float* __restrict__ data, uint32_t w, uint32_t h, uint32_t pitch, unsigned long long* __restrict__ first) {
+__global__ void k_dem_normalize(float* __restrict__ d, uint32_t w, uint32_t h, uint32_t pitch, int mode, float a, float scale, float lo) {
     const size_t n = (size_t)w * h;
-    unsigned long long best = ~0ull;
     for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
         const size_t r = idx / w, c = idx - r * w;
-        if (__ldg(data + r * pitch + c) == 0.0f) { best = idx; break; }      // a thread's indices ascend
-    }
-    if (best != ~0ull) atomicMin(first, best);
-}
-
-// replaces a zero extreme by the first zero of the image (sign included); out2 = (lo, hi)
-static int fix_zero_sign(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, float out2[2], cudaStream_t stream) {
-    if (out2[0] != 0.0f && out2[1] != 0.0f) return VF_OK;
-    unsigned long long* d_first = nullptr;
-    VF_CUDA(cudaMalloc(&d_first, 8));
-    unsigned long long first = ~0ull;
-    cudaError_t e = cudaMemcpyAsync(d_first, &first, 8, cudaMemcpyHostToDevice, stream);
-    if (e == cudaSuccess) {
-        const size_t n = (size_t)w * h;
-        const size_t blocks = (n + 255) / 256;
-        k_dem_first_zero<<<(int)(blocks > 148 * 16 ? 148 * 16 : blocks), 256, 0, stream>>>(d_data, w, h, pitch, d_first);
-        e = cudaMemcpyAsync(&first, d_first, 8, cudaMemcpyDeviceToHost, stream);
-    }
-    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    float z = 0.0f;
-    if (e == cudaSuccess && first != ~0ull)
-        e = cudaMemcpy(&z, d_data + (size_t)(first / w) * pitch + (size_t)(first % w), 4, cudaMemcpyDeviceToHost);
-    cudaFree(d_first);
-    VF_CUDA(e);
-    if (out2[0] == 0.0f) out2[0] = z;
-    if (out2[1] == 0.0f) out2[1] = z;
-    return VF_OK;
-}
-
-__global__ void k_dem_keys_to_float(const uint32_t* __restrict__ acc, float* __restrict__ out2) {
-    out2[0] = vf_key_float(acc[0]);
-    out2[1] = vf_key_float(acc[1]);
-}
-
-__global__ void k_dem_normalize(float* __restrict__ d, size_t n, int mode, float a, float scale, float lo) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        const float v = d[i];
+        float* p = d + r * pitch + c;
+        const float v = *p;
         // src/lib.rs:941 `(*v - min) * scale + lo` and :947 `(*v - mean) / denom` (no FMA in Rust)
-        d[i] = mode == 0 ? __fadd_rn(__fmul_rn(__fsub_rn(v, a), scale), lo) : __fdiv_rn(__fsub_rn(v, a), scale);
+        *p = mode == 0 ? __fadd_rn(__fmul_rn(__fsub_rn(v, a), scale), lo) : __fdiv_rn(__fsub_rn(v, a), scale);
     }
 }
-__global__ void k_dem_ingest_f64(const double* __restrict__ s, size_t n, float scale, float* __restrict__ d) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        d[i] = __fmul_rn((float)s[i], scale);      // src/lib.rs:384
+// f64 -> f32 cast and scale (src/lib.rs:384), f32 scale in place (src/lib.rs:362): rows of a pitched image
+__global__ void k_dem_ingest_f64(const double* __restrict__ s, size_t n, uint32_t w, uint32_t pitch, size_t first, float scale, float* __restrict__ d) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t idx = first + i, r = idx / w, c = idx - r * w;
+        d[r * pitch + c] = __fmul_rn((float)s[i], scale);
+    }
 }
-__global__ void k_dem_ingest_f32(const float* s, size_t n, float scale, float* d) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        d[i] = __fmul_rn(s[i], scale);             // src/lib.rs:362
+__global__ void k_dem_scale(float* __restrict__ d, uint32_t w, uint32_t h, uint32_t pitch, float scale) {
+    const size_t n = (size_t)w * h;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = idx / w, c = idx - r * w;
+        d[r * pitch + c] = __fmul_rn(d[r * pitch + c], scale);
+    }
 }
 
 static inline int grid_for(size_t n, int threads) {
     const size_t b = (n + threads - 1) / threads;
     return (int)(b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b));
 }
+static inline float key_to_float(uint32_t k) {
+    const uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+}
 
-struct DevBuf {
-    void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-};
+// accumulator block at the head of the scratch allocation (256 bytes): acc[4] | accd[2] | first | out2
+struct Moments { uint32_t acc[4]; double accd[2]; unsigned long long first; float out2[2]; };
+
+static int moments_begin(Moments* d_m, cudaStream_t st) {
+    Moments init;
+    memset(&init, 0, sizeof init);
+    init.acc[0] = 0xffffffffu; init.first = ~0ull;
+    VF_CUDA(cudaMemcpyAsync(d_m, &init, sizeof init, cudaMemcpyHostToDevice, st));   // (pageable source: staged before the call returns)
+    return VF_OK;
+}
+// min, max, mean, std from the accumulators; zero_value = the first zero of the data (sign included)
+static void moments_finish(const Moments& m, size_t n, float pivot, float zero_value, float out4[4]) {
+    out4[0] = key_to_float(m.acc[0]); out4[1] = key_to_float(m.acc[1]);
+    if (out4[0] == 0.0f) out4[0] = zero_value;
+    if (out4[1] == 0.0f) out4[1] = zero_value;
+    const double md = m.accd[0] / (double)n;
+    double var = m.accd[1] / (double)n - md * md;
+    if (var < 0.0) var = 0.0;
+    out4[2] = (float)((double)pivot + md);
+    out4[3] = (float)sqrt(var);
+}
+
+// statistics of a device-resident image -> (min, max, mean, std)
+static int stats_device(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, float out4[4], cudaStream_t st) {
+    const size_t n = (size_t)w * h;
+    Moments* d_m = (Moments*)vf_scratch(256);
+    if (!d_m) return VF_E_OOM;
+    float pivot = 0.0f;
+    VF_CUDA(cudaMemcpyAsync(&pivot, d_data, 4, cudaMemcpyDeviceToHost, st));
+    int rc = moments_begin(d_m, st);
+    if (rc) return rc;
+    VF_CUDA(cudaStreamSynchronize(st));
+    if (!isfinite(pivot)) pivot = 0.0f;
+    k_dem_moments<<<grid_for(n, 256), 256, 0, st>>>(d_data, w, h, pitch, 0ull, pivot, d_m->acc, d_m->accd, &d_m->first);
+    Moments m;
+    VF_CUDA(cudaMemcpyAsync(&m, d_m, sizeof m, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
+    VF_CUDA(cudaGetLastError());
+    float z = 0.0f;
+    if (m.first != ~0ull)
+        VF_CUDA(cudaMemcpy(&z, d_data + (size_t)(m.first / w) * pitch + (size_t)(m.first % w), 4, cudaMemcpyDeviceToHost));
+    moments_finish(m, n, pivot, z, out4);
+    return VF_OK;
+}
+
+// exact order statistics of m gathered values already on the device (vals) -> out2 (host)
+static int select_device(const float* d_vals, uint32_t m, float* d_out2, float out[2], cudaStream_t st) {
+    const uint32_t r1 = (uint32_t)((float)m * 0.01f), r99 = (uint32_t)((float)m * 0.99f);      // terrain_stats.rs:32-33
+    k_dem_select<<<1, 1024, 0, st>>>(d_vals, m, r1, r99, d_out2);
+    VF_CUDA(cudaMemcpyAsync(out, d_out2, 8, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
+    VF_CUDA(cudaGetLastError());
+    return VF_OK;
+}
+static void sample_plan(size_t n, size_t& step, size_t& m) {
+    const size_t SAMPLE = 65536;
+    step = 1; m = n;
+    if (n > SAMPLE) { step = n / SAMPLE; m = (n + step - 1) / step; }            // terrain_stats.rs:23-27
+}
 
 // (lo, hi) of a device-resident image.  clamp=1: percentile semantics of terrain_stats.rs:20-34.
 int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, int clamp,
                          float* lo, float* hi, cudaStream_t stream) {
     const size_t n = (size_t)w * h;
     if (n == 0) return vf_set_error(VF_E_INVALID, "heightmap slice empty");
-    DevBuf scratch;
-    float out[2];
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
     if (!clamp) {
-        VF_CUDA(cudaMalloc(&scratch.p, 64));
-        uint32_t* acc = (uint32_t*)scratch.p;
-        double* accd = (double*)((char*)scratch.p + 16);
-        float* o2 = (float*)((char*)scratch.p + 48);
-        const uint32_t init[4] = {0xffffffffu, 0u, 0u, 0u};
-        VF_CUDA(cudaMemcpyAsync(acc, init, 16, cudaMemcpyHostToDevice, stream));
-        VF_CUDA(cudaMemsetAsync(accd, 0, 32, stream));
-        k_dem_reduce<<<grid_for(n, 256), 256, 0, stream>>>(d_data, w, h, pitch, 0, 0.0, acc, accd);
-        k_dem_keys_to_float<<<1, 1, 0, stream>>>(acc, o2);
-        VF_CUDA(cudaMemcpyAsync(out, o2, 8, cudaMemcpyDeviceToHost, stream));
-        VF_CUDA(cudaStreamSynchronize(stream));
-        const int rc = fix_zero_sign(d_data, w, h, pitch, out, stream);
+        float st4[4];
+        const int rc = stats_device(d_data, w, h, pitch, st4, stream);
         if (rc) return rc;
-    } else {
-        const size_t SAMPLE = 65536;
-        size_t step = 1, m = n;
-        if (n > SAMPLE) { step = n / SAMPLE; m = (n + step - 1) / step; }   // terrain_stats.rs:23-27
-        const uint32_t r1 = (uint32_t)((float)m * 0.01f), r99 = (uint32_t)((float)m * 0.99f);  // :32-33
-        VF_CUDA(cudaMalloc(&scratch.p, m * 4 + 16));
-        float* vals = (float*)scratch.p;
-        float* o2 = vals + m;
-        k_dem_gather<<<grid_for(m, 256), 256, 0, stream>>>(d_data, w, pitch, step, (uint32_t)m, vals);
-        k_dem_select<<<1, 1024, 0, stream>>>(vals, (uint32_t)m, r1, r99, o2);
-        VF_CUDA(cudaMemcpyAsync(out, o2, 8, cudaMemcpyDeviceToHost, stream));
-        VF_CUDA(cudaStreamSynchronize(stream));
+        *lo = st4[0]; *hi = st4[1];
+        return VF_OK;
     }
-    VF_CUDA(cudaGetLastError());
+    size_t step, m;
+    sample_plan(n, step, m);
+    char* sc = (char*)vf_scratch(256 + m * 4);
+    if (!sc) return VF_E_OOM;
+    float* vals = (float*)(sc + 256);
+    float out[2];
+    k_dem_gather<<<grid_for(m, 256), 256, 0, stream>>>(d_data, w, pitch, step, (uint32_t)m, vals);
+    const int rc = select_device(vals, (uint32_t)m, (float*)sc, out, stream);
+    if (rc) return rc;
     *lo = out[0]; *hi = out[1];
     return VF_OK;
 }
 
-static int upload(const void* host, size_t bytes, DevBuf& b) {
-    VF_CUDA(cudaMalloc(&b.p, bytes ? bytes : 4));
-    VF_CUDA(cudaMemcpy(b.p, host, bytes, cudaMemcpyHostToDevice));
-    return VF_OK;
-}
+// ---- host-array entry points ---------------------------------------------------------------------------------
+// A flat host array is streamed through the scratch allocation in chunks (64 MiB): nothing is allocated per call,
+// and an array larger than the device's free memory still works.
+static const size_t kChunkFloats = 16u << 20;
+static int vf_dem_stats_locked(const float* data, size_t n, float out4[4], cudaStream_t st);
 
 extern "C" int vf_dem_minmax(const float* data, size_t n, int clamp, float* lo, float* hi) {
     if (!data || !lo || !hi) return vf_set_error(VF_E_INVALID, "null argument");
     if (n == 0) return vf_set_error(VF_E_INVALID, "heightmap slice empty");
-    if (n > 0xffffffffull) return vf_set_error(VF_E_INVALID, "more than 2^32 samples");
     int rc = vf_require_device();
     if (rc) return rc;
-    DevBuf d;
-    rc = upload(data, n * 4, d);
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    if (clamp) {
+        // terrain_stats.rs:23-27: the statistic is defined on the strided sample data[0], data[step], ...: those
+        // <= 65 537 values are staged in pinned memory (a memory-bound gather, no arithmetic) and 256 KB cross the bus
+        // instead of the whole array; the order statistics themselves are selected on the device.
+        size_t step, m;
+        sample_plan(n, step, m);
+        float* stage = (float*)vf_pinned_scratch(m * 4);
+        char* sc = (char*)vf_scratch(256 + m * 4);
+        if (!stage || !sc) return VF_E_OOM;
+        // (every sample is a cache and, at large strides, a TLB miss: software prefetch keeps ~32 of them in flight per
+        // thread, four threads share the work on large arrays)
+        auto gather = [&](size_t k0, size_t k1) {
+            for (size_t k = k0; k < k1; ++k) {
+                if (k + 32 < k1) __builtin_prefetch(data + (k + 32) * step, 0, 0);
+                stage[k] = data[k * step];
+            }
+        };
+        if (step >= 64 && m >= 16384) {
+            std::thread th[3];
+            for (int t = 0; t < 3; ++t) th[t] = std::thread(gather, m * (t + 1) / 4, m * (t + 2) / 4);
+            gather(0, m / 4);
+            for (auto& t : th) t.join();
+        } else {
+            gather(0, m);
+        }
+        float* vals = (float*)(sc + 256);
+        VF_CUDA(cudaMemcpyAsync(vals, stage, m * 4, cudaMemcpyHostToDevice, st));
+        float out[2];
+        rc = select_device(vals, (uint32_t)m, (float*)sc, out, st);
+        if (rc) return rc;
+        *lo = out[0]; *hi = out[1];
+        return VF_OK;
+    }
+    float st4[4];
+    rc = vf_dem_stats_locked(data, n, st4, st);
     if (rc) return rc;
-    // present the flat slice as rows of <= 65536 columns... a 1-row image keeps indices identical
-    return vf_dem_minmax_device((const float*)d.p, (uint32_t)n, 1, (uint32_t)n, clamp, lo, hi, 0);
+    *lo = st4[0]; *hi = st4[1];
+    return VF_OK;
 }
 
-static int stats_device(const float* d_data, uint32_t w, uint32_t h, uint32_t pitch, float out4[4]) {
-    const size_t n = (size_t)w * h;
-    DevBuf scratch;
-    VF_CUDA(cudaMalloc(&scratch.p, 64));
-    uint32_t* acc = (uint32_t*)scratch.p;
-    double* accd = (double*)((char*)scratch.p + 16);
-    const uint32_t init[4] = {0xffffffffu, 0u, 0u, 0u};
-    VF_CUDA(cudaMemcpy(acc, init, 16, cudaMemcpyHostToDevice));
-    VF_CUDA(cudaMemset(accd, 0, 32));
-    k_dem_reduce<<<grid_for(n, 256), 256>>>(d_data, w, h, pitch, 0, 0.0, acc, accd);
-    double hd[2];
-    uint32_t hk[2];
-    VF_CUDA(cudaMemcpy(hd, accd, 16, cudaMemcpyDeviceToHost));
-    VF_CUDA(cudaMemcpy(hk, acc, 8, cudaMemcpyDeviceToHost));
-    const double mean = hd[0] / (double)n;
-    k_dem_reduce<<<grid_for(n, 256), 256>>>(d_data, w, h, pitch, 1, mean, acc, accd);
-    VF_CUDA(cudaMemcpy(hd, accd, 16, cudaMemcpyDeviceToHost));
+// min / max / mean / std of a flat host array, chunked (the util mutex is held by the caller)
+static int vf_dem_stats_locked(const float* data, size_t n, float out4[4], cudaStream_t st) {
+    const size_t chunk = n < kChunkFloats ? n : kChunkFloats;
+    char* sc = (char*)vf_scratch(256 + chunk * 4);
+    if (!sc) return VF_E_OOM;
+    Moments* d_m = (Moments*)sc;
+    float* buf = (float*)(sc + 256);
+    int rc = moments_begin(d_m, st);
+    if (rc) return rc;
+    const float pivot = isfinite(data[0]) ? data[0] : 0.0f;
+    for (size_t off = 0; off < n; off += chunk) {
+        const size_t c = n - off < chunk ? n - off : chunk;
+        VF_CUDA(cudaMemcpyAsync(buf, data + off, c * 4, cudaMemcpyHostToDevice, st));      // stream order protects `buf`
+        k_dem_moments<<<grid_for(c, 256), 256, 0, st>>>(buf, (uint32_t)c, 1u, (uint32_t)c, (unsigned long long)off, pivot,
+                                                        d_m->acc, d_m->accd, &d_m->first);
+    }
+    Moments m;
+    VF_CUDA(cudaMemcpyAsync(&m, d_m, sizeof m, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
     VF_CUDA(cudaGetLastError());
-    auto kf = [](uint32_t k) { uint32_t b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k; float f; memcpy(&f, &b, 4); return f; };
-    out4[0] = kf(hk[0]); out4[1] = kf(hk[1]);
-    const int rcz = fix_zero_sign(d_data, w, h, pitch, out4, 0);
-    if (rcz) return rcz;
-    out4[2] = (float)mean;
-    out4[3] = (float)sqrt(hd[1] / (double)n);
+    moments_finish(m, n, pivot, m.first != ~0ull ? data[m.first] : 0.0f, out4);
     return VF_OK;
 }
 
 extern "C" int vf_dem_stats(const float* data, size_t n, float out4[4]) {
     if (!data || !out4) return vf_set_error(VF_E_INVALID, "null argument");
     if (n == 0) { out4[0] = out4[1] = out4[2] = out4[3] = 0.0f; return VF_OK; }   // src/lib.rs:906-908
-    if (n > 0xffffffffull) return vf_set_error(VF_E_INVALID, "more than 2^32 samples");
     int rc = vf_require_device();
     if (rc) return rc;
-    DevBuf d;
-    rc = upload(data, n * 4, d);
-    if (rc) return rc;
-    return stats_device((const float*)d.p, (uint32_t)n, 1, (uint32_t)n, out4);
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    return vf_dem_stats_locked(data, n, out4, st);
+}
+
+// normalisation parameters of src/lib.rs:936-949 from (min, max, mean, std)
+static void normalize_params(const float st[4], int mode, float eps, float lo, float hi, float& a, float& scale) {
+    if (mode == 0) {
+        float denom = fabsf(st[1] - st[0]);
+        if (!(denom > eps)) denom = eps;
+        scale = (hi - lo) / denom;
+        a = st[0];
+    } else {
+        scale = st[3] > eps ? st[3] : eps;
+        a = st[2];
+    }
 }
 
 extern "C" int vf_dem_normalize(float* data, size_t n, int mode, float eps, float lo, float hi) {
     if (!data) return vf_set_error(VF_E_INVALID, "null argument");
     if (mode != 0 && mode != 1) return vf_set_error(VF_E_INVALID, "mode must be 'minmax' or 'zscore'");
     if (n == 0) return VF_OK;
-    if (n > 0xffffffffull) return vf_set_error(VF_E_INVALID, "more than 2^32 samples");
     int rc = vf_require_device();
     if (rc) return rc;
-    DevBuf d;
-    rc = upload(data, n * 4, d);
-    if (rc) return rc;
-    float st[4];
-    rc = stats_device((const float*)d.p, (uint32_t)n, 1, (uint32_t)n, st);
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    float s4[4];
+    rc = vf_dem_stats_locked(data, n, s4, st);
     if (rc) return rc;
     float a, scale;
-    if (mode == 0) {                                   // src/lib.rs:936-943
-        float denom = fabsf(st[1] - st[0]);
-        if (!(denom > eps)) denom = eps;
-        scale = (hi - lo) / denom;
-        a = st[0];
-    } else {                                           // :944-949
-        scale = st[3] > eps ? st[3] : eps;
-        a = st[2];
+    normalize_params(s4, mode, eps, lo, hi, a, scale);
+    const size_t chunk = n < kChunkFloats ? n : kChunkFloats;
+    char* sc = (char*)vf_scratch(256 + chunk * 4);
+    if (!sc) return VF_E_OOM;
+    float* buf = (float*)(sc + 256);
+    for (size_t off = 0; off < n; off += chunk) {
+        const size_t c = n - off < chunk ? n - off : chunk;
+        VF_CUDA(cudaMemcpyAsync(buf, data + off, c * 4, cudaMemcpyHostToDevice, st));
+        k_dem_normalize<<<grid_for(c, 256), 256, 0, st>>>(buf, (uint32_t)c, 1u, (uint32_t)c, mode, a, scale, lo);
+        VF_CUDA(cudaMemcpyAsync(data + off, buf, c * 4, cudaMemcpyDeviceToHost, st));
     }
-    k_dem_normalize<<<grid_for(n, 256), 256>>>((float*)d.p, n, mode, a, scale, lo);
+    VF_CUDA(cudaStreamSynchronize(st));
     VF_CUDA(cudaGetLastError());
-    VF_CUDA(cudaMemcpy(data, d.p, n * 4, cudaMemcpyDeviceToHost));
     return VF_OK;
 }
 
+// ---- device-resident height images (vf_height): add_terrain without bouncing through the host ---------------------
+static int height_alloc(uint32_t w, uint32_t h, vf_height** out) {
+    vf_height* t = new vf_height();
+    t->w = w; t->h = h;
+    t->pitch = (((size_t)w * 4) + 15) & ~(size_t)15;
+    if (cudaGetDevice(&t->device) != cudaSuccess) t->device = 0;
+    const cudaError_t e = cudaMalloc(&t->d, t->pitch * h);
+    if (e != cudaSuccess) {
+        delete t;
+        (void)cudaGetLastError();
+        return vf_set_error(e == cudaErrorMemoryAllocation ? VF_E_OOM : VF_E_CUDA, "height image allocation: %s", cudaGetErrorString(e));
+    }
+    *out = t;
+    return VF_OK;
+}
+
+extern "C" int vf_height_ingest_f32(const float* host, uint32_t w, uint32_t h, float scale, vf_height** out) {
+    if (!host || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "heightmap cannot be empty");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    vf_height* t = nullptr;
+    rc = height_alloc(w, h, &t);
+    if (rc) return rc;
+    cudaError_t e = cudaMemcpy2DAsync(t->d, t->pitch, host, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice, st);
+    if (e == cudaSuccess && scale != 1.0f) {
+        k_dem_scale<<<grid_for((size_t)w * h, 256), 256, 0, st>>>(t->d, w, h, (uint32_t)(t->pitch / 4), scale);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { vf_height_destroy(t); return vf_set_error(VF_E_CUDA, "height ingest: %s", cudaGetErrorString(e)); }
+    *out = t;
+    return VF_OK;
+}
+
+extern "C" int vf_height_ingest_f64(const double* host, uint32_t w, uint32_t h, float scale, vf_height** out) {
+    if (!host || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "heightmap cannot be empty");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    vf_height* t = nullptr;
+    rc = height_alloc(w, h, &t);
+    if (rc) return rc;
+    const size_t n = (size_t)w * h, chunk = n < kChunkFloats / 2 ? n : kChunkFloats / 2;      // doubles: 64 MiB chunks
+    double* buf = (double*)vf_scratch(chunk * 8);
+    if (!buf) { vf_height_destroy(t); return VF_E_OOM; }
+    cudaError_t e = cudaSuccess;
+    for (size_t off = 0; off < n && e == cudaSuccess; off += chunk) {
+        const size_t c = n - off < chunk ? n - off : chunk;
+        e = cudaMemcpyAsync(buf, host + off, c * 8, cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) {
+            k_dem_ingest_f64<<<grid_for(c, 256), 256, 0, st>>>(buf, c, w, (uint32_t)(t->pitch / 4), off, scale, t->d);
+            e = cudaGetLastError();
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) { vf_height_destroy(t); return vf_set_error(VF_E_CUDA, "height ingest: %s", cudaGetErrorString(e)); }
+    *out = t;
+    return VF_OK;
+}
+
+extern "C" int vf_height_clone(const vf_height* src, vf_height** out) {
+    if (!src || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    VF_CUDA(cudaSetDevice(src->device));
+    vf_height* t = nullptr;
+    int rc = height_alloc(src->w, src->h, &t);
+    if (rc) return rc;
+    const cudaError_t e = cudaMemcpy(t->d, src->d, src->pitch * src->h, cudaMemcpyDeviceToDevice);
+    if (e != cudaSuccess) { vf_height_destroy(t); return vf_set_error(VF_E_CUDA, "height clone: %s", cudaGetErrorString(e)); }
+    *out = t;
+    return VF_OK;
+}
+
+extern "C" int vf_height_minmax(const vf_height* t, int clamp, float* lo, float* hi) {
+    if (!t || !lo || !hi) return vf_set_error(VF_E_INVALID, "null argument");
+    VF_CUDA(cudaSetDevice(t->device));
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    return vf_dem_minmax_device(t->d, t->w, t->h, (uint32_t)(t->pitch / 4), clamp, lo, hi, st);
+}
+
+extern "C" int vf_height_stats(const vf_height* t, float out4[4]) {
+    if (!t || !out4) return vf_set_error(VF_E_INVALID, "null argument");
+    VF_CUDA(cudaSetDevice(t->device));
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    return stats_device(t->d, t->w, t->h, (uint32_t)(t->pitch / 4), out4, st);
+}
+
+extern "C" int vf_height_normalize(vf_height* t, int mode, float eps, float lo, float hi) {
+    if (!t) return vf_set_error(VF_E_INVALID, "null argument");
+    if (mode != 0 && mode != 1) return vf_set_error(VF_E_INVALID, "mode must be 'minmax' or 'zscore'");
+    VF_CUDA(cudaSetDevice(t->device));
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    if (!st) return VF_E_CUDA;
+    float s4[4];
+    const int rc = stats_device(t->d, t->w, t->h, (uint32_t)(t->pitch / 4), s4, st);
+    if (rc) return rc;
+    float a, scale;
+    normalize_params(s4, mode, eps, lo, hi, a, scale);
+    k_dem_normalize<<<grid_for((size_t)t->w * t->h, 256), 256, 0, st>>>(t->d, t->w, t->h, (uint32_t)(t->pitch / 4), mode, a, scale, lo);
+    VF_CUDA(cudaGetLastError());
+    VF_CUDA(cudaStreamSynchronize(st));
+    return VF_OK;
+}
+
+// the one-shot host-to-host forms of the ingest (kept for hosts that want the scaled copy back)
 extern "C" int vf_dem_ingest_f64(const double* src, size_t n, float scale, float* dst) {
     if (!src || !dst) return vf_set_error(VF_E_INVALID, "null argument");
     if (n == 0) return VF_OK;
-    int rc = vf_require_device();
+    if (n > 0xffffffffull) return vf_set_error(VF_E_INVALID, "more than 2^32 samples");
+    vf_height* t = nullptr;
+    int rc = vf_height_ingest_f64(src, (uint32_t)n, 1u, scale, &t);
     if (rc) return rc;
-    DevBuf s, d;
-    rc = upload(src, n * 8, s);
-    if (rc) return rc;
-    VF_CUDA(cudaMalloc(&d.p, n * 4));
-    k_dem_ingest_f64<<<grid_for(n, 256), 256>>>((const double*)s.p, n, scale, (float*)d.p);
-    VF_CUDA(cudaGetLastError());
-    VF_CUDA(cudaMemcpy(dst, d.p, n * 4, cudaMemcpyDeviceToHost));
-    return VF_OK;
+    rc = vf_height_read_patch(t, 0, 0, (uint32_t)n, 1u, dst);
+    vf_height_destroy(t);
+    return rc;
 }
 
 extern "C" int vf_dem_ingest_f32(const float* src, size_t n, float scale, float* dst) {
     if (!src || !dst) return vf_set_error(VF_E_INVALID, "null argument");
     if (n == 0) return VF_OK;
-    int rc = vf_require_device();
+    if (n > 0xffffffffull) return vf_set_error(VF_E_INVALID, "more than 2^32 samples");
+    vf_height* t = nullptr;
+    int rc = vf_height_ingest_f32(src, (uint32_t)n, 1u, scale, &t);
     if (rc) return rc;
-    DevBuf s;
-    rc = upload(src, n * 4, s);
-    if (rc) return rc;
-    k_dem_ingest_f32<<<grid_for(n, 256), 256>>>((const float*)s.p, n, scale, (float*)s.p);
-    VF_CUDA(cudaGetLastError());
-    VF_CUDA(cudaMemcpy(dst, s.p, n * 4, cudaMemcpyDeviceToHost));
-    return VF_OK;
+    rc = vf_height_read_patch(t, 0, 0, (uint32_t)n, 1u, dst);
+    vf_height_destroy(t);
+    return rc;
 }

@@ -62,23 +62,21 @@ k_triangle(uint32_t W, uint32_t H, const float* __restrict__ thr_g, uint8_t* __r
     }
 }
 
-struct DevPtr {
-    void* p = nullptr;
-    ~DevPtr() { if (p) cudaFree(p); }
-};
-
 extern "C" int vf_triangle_render(int w, int h, uint8_t* out_rgba_host) {
     if (w <= 0 || h <= 0 || !out_rgba_host) return vf_set_error(VF_E_INVALID, "invalid size / null output");
     int rc = vf_require_device();
     if (rc) return rc;
-    DevPtr d;
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
     const size_t bytes = (size_t)w * h * 4;
-    VF_CUDA(cudaMalloc(&d.p, bytes));
+    uint8_t* d = (uint8_t*)vf_scratch(bytes);            // cached per device: no cudaMalloc / cudaFree per call
+    if (!st || !d) return VF_E_CUDA;
     const size_t groups = (size_t)((w + 3) / 4) * h;
     const int blocks = (int)((groups + 255) / 256 > 148 * 8 ? 148 * 8 : (groups + 255) / 256);
-    k_triangle<<<blocks, 256>>>((uint32_t)w, (uint32_t)h, vf_srgb_thresholds_dev(), (uint8_t*)d.p);
+    k_triangle<<<blocks, 256, 0, st>>>((uint32_t)w, (uint32_t)h, vf_srgb_thresholds_dev(), d);
     VF_CUDA(cudaGetLastError());
-    VF_CUDA(cudaMemcpy(out_rgba_host, d.p, bytes, cudaMemcpyDeviceToHost));
+    VF_CUDA(cudaMemcpyAsync(out_rgba_host, d, bytes, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
     return VF_OK;
 }
 
@@ -117,28 +115,24 @@ extern "C" int vf_grid_generate(uint32_t nx, uint32_t nz, float dx, float dy, fl
     int rc = vf_require_device();
     if (rc) return rc;
     const size_t n = (size_t)nx * nz, m = (size_t)(nx - 1) * (nz - 1) * 6;
-    DevPtr dxy, duv, didx;
-    VF_CUDA(cudaMalloc(&dxy.p, n * 8));
-    VF_CUDA(cudaMalloc(&duv.p, n * 8));
-    VF_CUDA(cudaMalloc(&didx.p, m * 4));
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    const size_t o_uv = (n * 8 + 255) & ~(size_t)255, o_idx = o_uv + ((n * 8 + 255) & ~(size_t)255);
+    char* d = (char*)vf_scratch(o_idx + m * 4);          // one cached allocation: xy | uv | indices
+    if (!st || !d) return VF_E_CUDA;
     const size_t b = (n + 255) / 256;
-    k_grid<<<(int)(b > 148 * 16 ? 148 * 16 : b), 256>>>(nx, nz, dx, dy, (float2*)dxy.p, (float2*)duv.p, (uint32_t*)didx.p);
+    k_grid<<<(int)(b > 148 * 16 ? 148 * 16 : b), 256, 0, st>>>(nx, nz, dx, dy, (float2*)d, (float2*)(d + o_uv), (uint32_t*)(d + o_idx));
     VF_CUDA(cudaGetLastError());
-    VF_CUDA(cudaMemcpy(xy, dxy.p, n * 8, cudaMemcpyDeviceToHost));
-    VF_CUDA(cudaMemcpy(uv, duv.p, n * 8, cudaMemcpyDeviceToHost));
-    VF_CUDA(cudaMemcpy(idx, didx.p, m * 4, cudaMemcpyDeviceToHost));
+    VF_CUDA(cudaMemcpyAsync(xy, d, n * 8, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaMemcpyAsync(uv, d + o_uv, n * 8, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaMemcpyAsync(idx, d + o_idx, m * 4, cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
     return VF_OK;
 }
 
 // ---------------------------------------------------------------------------------------
 // R32F height image: src/lib.rs:496-681.  wgpu's 256-byte row padding has no equivalent here:
 // the image is a pitched device allocation and patches come back with cudaMemcpy2D.
-struct vf_height {
-    float* d = nullptr;
-    uint32_t w = 0, h = 0;
-    size_t pitch = 0;      // bytes
-};
-
 extern "C" int vf_height_upload(const float* host, uint32_t w, uint32_t h, vf_height** out) {
     if (!host || !out) return vf_set_error(VF_E_INVALID, "null argument");
     if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "terrain dimensions are zero");
@@ -147,6 +141,7 @@ extern "C" int vf_height_upload(const float* host, uint32_t w, uint32_t h, vf_he
     vf_height* t = new vf_height();
     t->w = w; t->h = h;
     t->pitch = (((size_t)w * 4) + 15) & ~(size_t)15;
+    if (cudaGetDevice(&t->device) != cudaSuccess) t->device = 0;
     cudaError_t e = cudaMalloc(&t->d, t->pitch * h);
     if (e == cudaSuccess)
         e = cudaMemcpy2D(t->d, t->pitch, host, (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice);

@@ -6,10 +6,12 @@
 #include <string.h>
 
 #include <algorithm>
+#include <chrono>
 #include <vector>
 
 #include "vf_internal.h"
 #include "vf_geom_march.cuh"
+#include "vf_png_dev.h"
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
 typedef CUresult (*vf_tmap_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -103,11 +105,52 @@ struct vf_scene {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_done[2] = {nullptr, nullptr}, ev_copied[2] = {nullptr, nullptr};
+    // PNG output encoded on the device (vf_png_dev.cu): created on first use; VF_PNG_SLOTS finished files can wait
+    // in HBM for their (size-exact) copies while later frames render
+    VfPngDev* png = nullptr;
+    uint32_t* h_png_size = nullptr;                       // pinned, one per file slot
+    cudaEvent_t ev_png_done[4] = {nullptr, nullptr, nullptr, nullptr}, ev_png_copied[4] = {nullptr, nullptr, nullptr, nullptr};
+    bool png_slot_used[4] = {false, false, false, false};
+    float encode_ms = 0.0f;
     bool timing = false;
     vf_frame_stats_t stats;
+    // render_metrics(): one set of timing events per synchronous call / per ticket, byte counters, wall clock
+    struct Marks { cudaEvent_t g0 = nullptr, g1 = nullptr, r0 = nullptr, r1 = nullptr; bool copies = false; int frames = 0; uint64_t d2h = 0;
+                   std::chrono::steady_clock::time_point t0; };
+    Marks marks, ticket_marks[4];
+    cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr; cudaStream_t up_stream_of_events = nullptr; bool upload_timed = false;
+    uint64_t h2d_bytes = 0, d2h_bytes = 0, last_h2d_bytes = 0;
+    vf_render_metrics_t metrics;
 };
 
 static const int VF_MAX_SLOTS = 2;
+
+static int marks_init(vf_scene::Marks& m) {
+    if (m.g0) return VF_OK;
+    VF_CUDA(cudaEventCreate(&m.g0)); VF_CUDA(cudaEventCreate(&m.g1));
+    VF_CUDA(cudaEventCreate(&m.r0)); VF_CUDA(cudaEventCreate(&m.r1));
+    return VF_OK;
+}
+static void marks_free(vf_scene::Marks& m) {
+    for (cudaEvent_t e : {m.g0, m.g1, m.r0, m.r1}) if (e) cudaEventDestroy(e);
+    m.g0 = m.g1 = m.r0 = m.r1 = nullptr;
+}
+// device memory the scene holds right now
+static uint64_t scene_vram_bytes(const vf_scene* s) {
+    const uint64_t img = (uint64_t)s->pitch * s->Hd * 4, hg = (uint64_t)s->hpitch * s->G * 4, hm = (uint64_t)s->hmm_nb * s->hmm_nb * 8;
+    uint64_t b = 0;
+    b += s->d_dem ? img : 0; b += s->d_dem_back ? img : 0;
+    b += s->d_hgrid ? hg : 0; b += s->d_hgrid_back ? hg : 0;
+    b += s->d_hmm ? hm : 0; b += s->d_hmm_back ? hm : 0;
+    b += (uint64_t)s->G * sizeof(VfAxis) + 256 * sizeof(float4);
+    b += (uint64_t)s->n_slots * s->W * s->H * 4;                       // frame slots
+    b += (uint64_t)s->W * s->H * 8;                                    // visibility buffer
+    b += s->d_vis ? (uint64_t)s->W * s->H * 4 : 0;
+    b += ((uint64_t)s->n_tiles + VF_CNT_WORDS) * 4 + ((uint64_t)s->n_tiles + 5) * 4 + (uint64_t)s->n_tiles * 4;
+    b += 3ull * s->capacity * 4 + (uint64_t)s->big_capacity * 4 + (uint64_t)s->segtab_cap * 8;
+    b += vf_png_dev_bytes(s->png);
+    return b;
+}
 
 static void scene_free(vf_scene* s) {
     if (!s) return;
@@ -120,6 +163,14 @@ static void scene_free(vf_scene* s) {
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
     if (s->ev_front_released) cudaEventDestroy(s->ev_front_released);
     for (auto& t : s->tickets) if (t.done) cudaEventDestroy(t.done);
+    marks_free(s->marks);
+    for (auto& m : s->ticket_marks) marks_free(m);
+    vf_png_dev_destroy(s->png);
+    if (s->h_png_size) cudaFreeHost(s->h_png_size);
+    for (auto& e : s->ev_png_done) if (e) cudaEventDestroy(e);
+    for (auto& e : s->ev_png_copied) if (e) cudaEventDestroy(e);
+    if (s->ev_up0) cudaEventDestroy(s->ev_up0);
+    if (s->ev_up1) cudaEventDestroy(s->ev_up1);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     for (auto& e : s->ev) if (e) cudaEventDestroy(e);
     for (auto& e : s->ev_done) if (e) cudaEventDestroy(e);
@@ -251,7 +302,11 @@ static int scene_bind(const vf_scene* s) {
     return VF_OK;
 }
 
-static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
+// `src`: w x h floats, rows `src_pitch` bytes apart, in host memory (kind = cudaMemcpyHostToDevice) or on the scene's
+// device (cudaMemcpyDeviceToDevice: a vf_height image, no PCIe crossing)
+static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t h, size_t src_pitch = 0,
+                            cudaMemcpyKind kind = cudaMemcpyHostToDevice) {
+    if (!src_pitch) src_pitch = (size_t)w * 4;
     if (w == 0 || h == 0) return vf_set_error(VF_E_INVALID, "height image cannot be empty");
     const uint32_t pitch = (w + 3u) & ~3u;            // rows start 16-byte aligned (TMA-ready)
     if (int rcb = scene_bind(s)) return rcb;
@@ -265,8 +320,11 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
         VF_CUDA(cudaMalloc(&s->d_dem, (size_t)pitch * h * 4));
     }
     s->Wd = w; s->Hd = h; s->pitch = pitch;
-    VF_CUDA(cudaMemcpy2DAsync(s->d_dem, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
-                              cudaMemcpyHostToDevice, s->stream));
+    if (!s->ev_up0) { VF_CUDA(cudaEventCreate(&s->ev_up0)); VF_CUDA(cudaEventCreate(&s->ev_up1)); }
+    VF_CUDA(cudaEventRecord(s->ev_up0, s->stream));
+    VF_CUDA(cudaMemcpy2DAsync(s->d_dem, (size_t)pitch * 4, host, src_pitch, (size_t)w * 4, h, kind, s->stream));
+    s->last_h2d_bytes = kind == cudaMemcpyHostToDevice ? (uint64_t)w * h * 4 : 0;
+    s->h2d_bytes += s->last_h2d_bytes;
     int rc = scene_rebuild_axis(s);
     if (rc) return rc;
     // TMA staging of the geometry pass: over the DEM itself when every grid index fetches the texel of the same
@@ -321,7 +379,9 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
         cudaFree(s->d_hmm); cudaFree(s->d_hmm_back);
         s->d_hmm = s->d_hmm_back = nullptr; s->hmm_nb = 0;
     }
+    VF_CUDA(cudaEventRecord(s->ev_up1, s->stream));
     VF_CUDA(cudaStreamSynchronize(s->stream));
+    s->upload_timed = true;
     return VF_OK;
 }
 
@@ -343,6 +403,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
     if (rc) return rc;
     vf_scene* s = new vf_scene();
     memset(&s->stats, 0, sizeof s->stats);
+    memset(&s->metrics, 0, sizeof s->metrics);
     memset(s->u44, 0, sizeof s->u44);
     s->W = w; s->H = h; s->G = grid; s->lut_id = lut_id; s->lut_unorm = lut_unorm;
     s->tiles_x = (uint32_t)(w + VF_TILE - 1) / VF_TILE;
@@ -405,6 +466,12 @@ extern "C" void vf_scene_destroy(vf_scene* s) {
 extern "C" int vf_scene_set_height_f32(vf_scene* s, const float* host, uint32_t w, uint32_t h) {
     if (!s || !host) return vf_set_error(VF_E_INVALID, "null argument");
     return scene_upload_dem(s, host, w, h);
+}
+
+extern "C" int vf_scene_set_height_image(vf_scene* s, const vf_height* t) {
+    if (!s || !t) return vf_set_error(VF_E_INVALID, "null argument");
+    if (t->device != s->device) return vf_set_error(VF_E_INVALID, "height image lives on device %d, the scene on device %d", t->device, s->device);
+    return scene_upload_dem(s, t->d, t->w, t->h, t->pitch, cudaMemcpyDeviceToDevice);
 }
 
 extern "C" int vf_scene_set_uniforms(vf_scene* s, const float u44[44]) {
@@ -623,6 +690,32 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     return VF_OK;
 }
 
+// after the call's work has completed: fold its marks into the metrics block
+static void scene_finish_metrics(vf_scene* s, vf_scene::Marks& mk) {
+    vf_render_metrics_t& m = s->metrics;
+    m.gpu_ms = m.readback_ms = 0.0f;
+    if (mk.g0 && cudaEventElapsedTime(&m.gpu_ms, mk.g0, mk.g1) != cudaSuccess) { (void)cudaGetLastError(); m.gpu_ms = 0.0f; }
+    if (mk.copies && cudaEventElapsedTime(&m.readback_ms, mk.r0, mk.r1) != cudaSuccess) { (void)cudaGetLastError(); m.readback_ms = 0.0f; }
+    m.total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - mk.t0).count();
+    m.frames = (uint32_t)mk.frames;
+    m.last_d2h_bytes = mk.d2h;
+    s->d2h_bytes += mk.d2h;
+}
+
+extern "C" int vf_scene_metrics(const vf_scene* sc, vf_render_metrics_t* out) {
+    if (!sc || !out) return vf_set_error(VF_E_INVALID, "null argument");
+    vf_scene* s = const_cast<vf_scene*>(sc);
+    if (s->upload_timed && s->ev_up0 && cudaEventQuery(s->ev_up1) == cudaSuccess) {
+        if (cudaEventElapsedTime(&s->metrics.upload_ms, s->ev_up0, s->ev_up1) != cudaSuccess) (void)cudaGetLastError();
+    } else {
+        (void)cudaGetLastError();
+    }
+    s->metrics.h2d_bytes = s->h2d_bytes; s->metrics.d2h_bytes = s->d2h_bytes; s->metrics.last_h2d_bytes = s->last_h2d_bytes;
+    s->metrics.vram_bytes = scene_vram_bytes(s);
+    *out = s->metrics;
+    return VF_OK;
+}
+
 static int scene_finish_stats(vf_scene* s) {
     s->stats.bin_pairs = s->h_counters_last[VF_CNT_PAIRS];
     s->stats.clipped_prims = s->h_counters_last[VF_CNT_CLIPPED];
@@ -654,11 +747,43 @@ static int scene_apply_pending_dem(vf_scene* s) {
 // Enqueues n frames (+ their D2H copies when out_host is given) and the read-back of the batch's
 // counters into pinned slot `hslot`.  Frame k is rendered into slot k%2 while the copy stream
 // drains the other slot to the host.  Does not wait.
+static const int VF_PNG_SLOTS = 3;
+struct VfPngOut { uint8_t* out; size_t cap; uint32_t* sizes; };          // n files of at most `cap` bytes each, sizes[k] bytes used
+
+// file `j` of a PNG batch has been encoded into its slot: read its size, start the size-exact copy to the host
+static int png_collect(vf_scene* s, const VfPngOut& po, int j, vf_scene::Marks& mk) {
+    const int ps = j % VF_PNG_SLOTS;
+    VF_CUDA(cudaEventSynchronize(s->ev_png_done[ps]));
+    const uint32_t size = s->h_png_size[ps];
+    if (size == 0xffffffffu || size > po.cap)
+        return vf_set_error(VF_E_INVALID, "PNG file %d needs %u bytes, the output slot holds %zu (size it with vf_png_file_bound)", j, size, po.cap);
+    po.sizes[j] = size;
+    if (!mk.copies) { VF_CUDA(cudaEventRecord(mk.r0, s->copy_stream)); mk.copies = true; }
+    VF_CUDA(cudaMemcpyAsync(po.out + (size_t)j * po.cap, s->png->d_files + (size_t)ps * s->png->file_cap, size, cudaMemcpyDeviceToHost, s->copy_stream));
+    VF_CUDA(cudaEventRecord(s->ev_png_copied[ps], s->copy_stream));
+    s->png_slot_used[ps] = true;
+    mk.d2h += size;
+    return VF_OK;
+}
+
 static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, int hslot,
-                        bool apply_pending = true) {
+                        bool apply_pending, vf_scene::Marks& mk, const VfPngOut* png_out = nullptr) {
     int rc = apply_pending ? scene_apply_pending_dem(s) : VF_OK;
     if (rc) return rc;
+    rc = marks_init(mk);
+    if (rc) return rc;
+    if (png_out && !s->png) {
+        rc = vf_png_dev_create(s->W, s->H, VF_PNG_SLOTS, &s->png);
+        if (rc) return rc;
+        VF_CUDA(cudaHostAlloc(&s->h_png_size, 4 * sizeof(uint32_t), cudaHostAllocDefault));
+        for (int k = 0; k < VF_PNG_SLOTS; ++k) {
+            VF_CUDA(cudaEventCreateWithFlags(&s->ev_png_done[k], cudaEventDisableTiming));
+            VF_CUDA(cudaEventCreateWithFlags(&s->ev_png_copied[k], cudaEventDisableTiming));
+        }
+    }
     const size_t fbytes = (size_t)s->W * s->H * 4;
+    mk.t0 = std::chrono::steady_clock::now(); mk.copies = false; mk.frames = n; mk.d2h = out_host ? (uint64_t)n * fbytes : 0;
+    VF_CUDA(cudaEventRecord(mk.g0, s->stream));
     VF_CUDA(cudaMemsetAsync(s->d_maxpairs, 0, 16, s->stream));
     s->submit_skipped_bins = false;
     for (int k = 0; k < n; ++k) {
@@ -671,12 +796,29 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         if (out_host) {
             VF_CUDA(cudaEventRecord(s->ev_done[slot], s->stream));
             VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[slot], 0));
+            if (!mk.copies) { VF_CUDA(cudaEventRecord(mk.r0, s->copy_stream)); mk.copies = true; }
             VF_CUDA(cudaMemcpyAsync(out_host + (size_t)k * fbytes, s->d_frame + (size_t)slot * fbytes,
                                     fbytes, cudaMemcpyDeviceToHost, s->copy_stream));
             VF_CUDA(cudaEventRecord(s->ev_copied[slot], s->copy_stream));
             s->slot_used[slot] = true;
         }
+        if (png_out) {
+            // frame k -> .png bytes in file slot k % VF_PNG_SLOTS (two kernels behind k_raster on the render stream), its
+            // size into pinned memory; the file of frame k - (VF_PNG_SLOTS - 1) is collected meanwhile, so the host's
+            // wait for a size never stalls the render stream
+            const int ps = k % VF_PNG_SLOTS;
+            if (s->png_slot_used[ps]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_png_copied[ps], 0));
+            rc = vf_png_dev_encode(s->png, s->d_frame + (size_t)slot * fbytes, ps, s->stream);
+            if (rc) return rc;
+            VF_CUDA(cudaMemcpyAsync(&s->h_png_size[ps], s->png->d_file_size + ps, 4, cudaMemcpyDeviceToHost, s->stream));
+            VF_CUDA(cudaEventRecord(s->ev_png_done[ps], s->stream));
+            if (k >= VF_PNG_SLOTS - 1) { rc = png_collect(s, *png_out, k - (VF_PNG_SLOTS - 1), mk); if (rc) return rc; }
+        }
     }
+    if (png_out)
+        for (int j = std::max(0, n - (VF_PNG_SLOTS - 1)); j < n; ++j) { rc = png_collect(s, *png_out, j, mk); if (rc) return rc; }
+    VF_CUDA(cudaEventRecord(mk.g1, s->stream));
+    if (mk.copies) VF_CUDA(cudaEventRecord(mk.r1, s->copy_stream));
     uint32_t* h = s->h_counters + (size_t)hslot * 2 * VF_CNT_WORDS;
     VF_CUDA(cudaMemcpyAsync(h, s->d_counters, VF_CNT_WORDS * 4, cudaMemcpyDeviceToHost, s->stream));
     VF_CUDA(cudaMemcpyAsync(h + VF_CNT_WORDS, s->d_maxpairs, 16, cudaMemcpyDeviceToHost, s->stream));
@@ -711,15 +853,17 @@ static int scene_check_overflow(vf_scene* s, int hslot, bool skipped_bins) {
 // Renders n frames and waits; out_host may be null (frames stay on the device).  If a kernel asked
 // for more queue / pair space than its buffer holds, the buffer is grown and the call is repeated
 // (an overflowed frame leaves a clean visibility buffer: k_raster always runs to completion).
-static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, bool apply_pending = true) {
+static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, bool apply_pending = true,
+                        const VfPngOut* png_out = nullptr) {
     if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
     int rc = scene_bind(s);
     if (rc) return rc;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending);
+        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending, s->marks, png_out);
         if (rc) return rc;
         VF_CUDA(cudaStreamSynchronize(s->stream));
-        if (out_host) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
+        if (out_host || png_out) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
+        scene_finish_metrics(s, s->marks);
         memcpy(s->h_counters_last, s->h_counters, VF_CNT_WORDS * 4);
         const int ov = scene_check_overflow(s, 0, s->submit_skipped_bins);
         if (ov < 0) return -ov;
@@ -744,6 +888,7 @@ static int ticket_resolve(vf_scene* s, int id) {
     t.resolved = true;
     t.rc = VF_OK;
     if (cudaEventSynchronize(t.done) != cudaSuccess) return t.rc = vf_set_error(VF_E_CUDA, "batch %d: %s", id, cudaGetErrorString(cudaGetLastError()));
+    scene_finish_metrics(s, s->ticket_marks[id]);
     const uint32_t* h = s->h_counters + (size_t)(1 + id) * 2 * VF_CNT_WORDS + VF_CNT_WORDS;
     if (h[0] <= t.cap_pairs && std::max(h[1], h[2]) <= t.cap_big && !(t.skipped_bins && h[2] > 0)) {
         if (h[2] > 0) s->bin_hold = s->bin_hold_len;
@@ -798,6 +943,9 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
     scene_resolve_readers(s, s->d_dem_back);      // normally none: those batches were collected long ago
     // the back image was the front image of frames submitted before the last swap
     if (s->front_released_once) VF_CUDA(cudaStreamWaitEvent(s->upload_stream, s->ev_front_released, 0));
+    if (!s->ev_up0) { VF_CUDA(cudaEventCreate(&s->ev_up0)); VF_CUDA(cudaEventCreate(&s->ev_up1)); }
+    VF_CUDA(cudaEventRecord(s->ev_up0, s->upload_stream));
+    s->last_h2d_bytes = (uint64_t)w * h * 4; s->h2d_bytes += s->last_h2d_bytes;
     VF_CUDA(cudaMemcpy2DAsync(s->d_dem_back, (size_t)pitch * 4, host, (size_t)w * 4, (size_t)w * 4, h,
                               cudaMemcpyHostToDevice, s->upload_stream));
     if (s->d_hgrid_back) {                        // vertex heights of the new image, behind its upload
@@ -808,6 +956,8 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
         launch_hminmax(s, s->d_dem_back, s->d_hgrid_back, s->d_hmm_back, s->upload_stream);
         VF_CUDA(cudaGetLastError());
     }
+    VF_CUDA(cudaEventRecord(s->ev_up1, s->upload_stream));
+    s->upload_timed = true;
     VF_CUDA(cudaEventRecord(s->ev_uploaded, s->upload_stream));
     s->back_pending = true;
     return VF_OK;
@@ -823,7 +973,7 @@ extern "C" int vf_scene_render_batch_async(vf_scene* s, const float* u44xn, int 
     vf_scene::Ticket& t = s->tickets[id];
     if (!t.done) VF_CUDA(cudaEventCreateWithFlags(&t.done, cudaEventDisableTiming));
     t.u.assign(u44xn, u44xn + (size_t)n * 44); t.n = n; t.out = out_rgba_host;
-    rc = scene_submit(s, u44xn, n, out_rgba_host, nullptr, 1 + id);
+    rc = scene_submit(s, u44xn, n, out_rgba_host, nullptr, 1 + id, true, s->ticket_marks[id]);
     if (rc) return rc;
     t.cap_pairs = s->capacity; t.cap_big = s->big_capacity; t.dem = s->d_dem;       // after the swap inside scene_submit
     t.skipped_bins = s->submit_skipped_bins;
@@ -854,6 +1004,14 @@ extern "C" int vf_scene_render_rgba(vf_scene* s, uint8_t* out_rgba_host) {
 extern "C" int vf_scene_render_batch(vf_scene* s, const float* u44xn, int n, uint8_t* out_rgba_host) {
     if (!s || !out_rgba_host) return vf_set_error(VF_E_INVALID, "null argument");
     return scene_render(s, u44xn, n, out_rgba_host, nullptr);
+}
+
+extern "C" size_t vf_png_file_bound(int w, int h) { return (w > 0 && h > 0) ? vf_png_dev_bound(w, h) : 0; }
+
+extern "C" int vf_scene_render_batch_png(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, size_t cap_per_file, uint32_t* sizes) {
+    if (!s || !out_host || !sizes) return vf_set_error(VF_E_INVALID, "null argument");
+    const VfPngOut po = {out_host, cap_per_file, sizes};
+    return scene_render(s, u44xn ? u44xn : s->u44, n, nullptr, nullptr, true, &po);
 }
 
 extern "C" int vf_scene_render_device(vf_scene* s, const float* u44xn, int n) {

@@ -81,11 +81,35 @@ def grid_generate(nx: int, nz: int, spacing=(1.0, 1.0), origin="center"):
 
 generate_grid = grid_generate                # legacy alias (reference :172)
 
+
+def report_environment() -> dict:
+    """Environment report for bug reports and bench logs (planned in the reference, ROADMAP.md:1989-1999: OS, Python,
+    package version, adapter name / backend / limits / features, library versions).  The backend here is CUDA; the
+    adapter dictionaries have the shape of enumerate_adapters() (reference src/lib.rs:744-845)."""
+    import os
+    import platform
+    import sys
+    drv, rt = _ext.cuda_versions()
+    fmt = lambda v: f"{v // 1000}.{(v % 1000) // 10}" if v else None   # noqa: E731
+    try:
+        adapters = list(enumerate_adapters())
+    except RuntimeError:
+        adapters = []
+    return {
+        "os": {"system": platform.system(), "release": platform.release(), "machine": platform.machine()},
+        "python": sys.version.split()[0], "executable": sys.executable, "numpy": _np.__version__,
+        "package": "vulkan_forge", "package_version": __version__, "backend": "CUDA (sm_100a kernels, no graphics API)",
+        "adapters": adapters, "cuda_driver_version": fmt(drv), "cuda_runtime_version": fmt(rt),
+        "native_library": os.path.join(os.path.dirname(os.path.abspath(__file__)), "libvfcuda.so"),
+        "build": _ext.build_info(),
+        "env": {k: os.environ[k] for k in ("CUDA_VISIBLE_DEVICES", "LOCAL_RANK", "VF_FORCE_LUT_UNORM", "VF_DISABLE_TMA") if k in os.environ},
+    }
+
 from .orbit import bind_host_to_gpu, orbit_cameras, render_orbit, shard_range  # noqa: E402  (additive multi-GPU helper)
 
 __all__ = [
     "Renderer", "TerrainSpike", "render_triangle_rgba", "render_triangle_png", "make_terrain",
     "colormap_supported", "camera_look_at", "camera_perspective", "camera_view_proj",
     "dem_stats", "dem_normalize", "grid_generate", "generate_grid", "__version__",
-    "Scene", "enumerate_adapters", "device_probe", "orbit_cameras", "render_orbit", "shard_range", "bind_host_to_gpu",
+    "Scene", "enumerate_adapters", "device_probe", "report_environment", "orbit_cameras", "render_orbit", "shard_range", "bind_host_to_gpu",
 ]

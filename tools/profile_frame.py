@@ -26,4 +26,4 @@ print("config", cfg, "frames", n, "ms", round(ms, 3), "ms/frame", round(ms / n, 
 sc.enable_timing(True)
 for k in (0, 5, 11):
     sc.render_batch_device(cams[k:k + 1])
-    print(k, {a: (round(v, 4) if isinstance(v, float) else v) for a, v in sc.render_metrics().items()})
+    m = sc.render_metrics(); print(k, {a: round(m[a], 4) for a in ("ms_geom", "ms_bin", "ms_raster", "ms_total", "gpu_ms")})

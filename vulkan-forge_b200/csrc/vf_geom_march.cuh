@@ -157,7 +157,7 @@ __device__ __forceinline__ void vf_gm_drain_long(const VfFrame& f, VfGmWarpT<DEP
             vf_edges_setup(t, x0, y0, es);
             const float rinv = DEPTH ? vf_gm_rinv(vf_area2(t)) : 0.0f;
             vf_thin_raster32(es, x0, x1, y0, y1, f.W, [&](bool covered, uint32_t idx, uint32_t e0, uint32_t e1, uint32_t e2) {
-                if (!DEPTH) { vf_vis_max_if(covered, vis + idx, prim); return; }
+                if (!DEPTH) { vf_vis_max_if(covered, reinterpret_cast<uint32_t*>(vis) + idx, prim); return; }
                 if (covered) vf_gm_emit_depth(vis + idx, t, rinv, es.nbias, prim, e0, e1, e2);
             });
         }
@@ -237,7 +237,7 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
             uint32_t idx = (uint32_t)y0 * f.W + (uint32_t)x0;                   // sample index in the frame
             const float rinv = DEPTH ? vf_gm_rinv(area2) : 0.0f;
             if (!DEPTH) {
-                vf_vis_max_if(micro && (e0 | e1 | e2) >= 0, vis + idx, prim);
+                vf_vis_max_if(micro && (e0 | e1 | e2) >= 0, reinterpret_cast<uint32_t*>(vis) + idx, prim);
             } else if (micro && (e0 | e1 | e2) >= 0) {
                 vf_gm_emit_depth(vis + idx, t, rinv, nbias, prim, (uint32_t)e0, (uint32_t)e1, (uint32_t)e2);
             }
@@ -255,7 +255,7 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                     dy += wrap ? 1 : 0;
                     const bool covered = (e0 | e1 | e2) >= 0;
                     if (!DEPTH) {
-                        vf_vis_max_if(covered, vis + idx, prim);
+                        vf_vis_max_if(covered, reinterpret_cast<uint32_t*>(vis) + idx, prim);
                     } else if (covered) {
                         vf_gm_emit_depth(vis + idx, t, rinv, nbias, prim, (uint32_t)e0, (uint32_t)e1, (uint32_t)e2);
                     }

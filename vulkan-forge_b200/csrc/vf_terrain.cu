@@ -69,6 +69,7 @@ struct vf_scene {
     // heights with it and skips the per-vertex clip tests where the task's box is provably inside the guard band
     float2* d_hmm = nullptr; float2* d_hmm_back = nullptr; uint32_t hmm_nb = 0;
     bool use_tma = false;                // texels of the geometry pass are staged with TMA
+    bool dem_identity = false;           // grid == DEM and every grid index fetches the texel of the same index
     bool geom_tiled = false;             // VF_GEOM_TILED at creation: tiled k_geom instead of k_geom_march (A/B runs)
     // back DEM image for vf_scene_set_height_f32_async: uploaded on upload_stream while frames of the
     // front image render; swapped in by the next submit
@@ -331,6 +332,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
     // index (checked on the device: f32 rounding of u*W can break it near the upper end at large sizes, SURVEY
     // 7.3-5), otherwise over the G x G image of vertex heights resampled here once
     s->use_tma = false;
+    s->dem_identity = false;
     memset(&s->dem_map, 0, sizeof s->dem_map);
     memset(s->dem_map_gm, 0, sizeof s->dem_map_gm);
     const uint64_t hbytes = (uint64_t)((s->G + 3u) & ~3u) * s->G * 4u;
@@ -344,6 +346,7 @@ static int scene_upload_dem(vf_scene* s, const float* host, uint32_t w, uint32_t
             VF_CUDA(cudaMemcpyAsync(&flag, s->d_flag, 4, cudaMemcpyDeviceToHost, s->stream));
             VF_CUDA(cudaStreamSynchronize(s->stream));
         }
+        s->dem_identity = flag == 1u;
         if (flag == 1u) {
             cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back);
             s->d_hgrid = s->d_hgrid_back = nullptr; s->hpitch = 0;
@@ -540,6 +543,7 @@ static void build_frame(const vf_scene* s, const float* u, VfFrame* f) {
     f->tiles_x = s->tiles_x; f->tiles_y = s->tiles_y;
     f->mode = s->mode; f->depth = s->depth;
     const float* P = f->P; const float* V = f->V;
+    f->gm_inv = s->G > 2 ? (uint32_t)((1ull << 32) / (s->G - 1)) : 0xffffffffu;
     f->sparse = (P[1] == 0 && P[2] == 0 && P[3] == 0 && P[4] == 0 && P[6] == 0 && P[7] == 0 && P[8] == 0 &&
                  P[9] == 0 && P[12] == 0 && P[13] == 0 && V[3] == 0 && V[7] == 0 && V[11] == 0 && V[15] == 1.0f) ? 1 : 0;
 }
@@ -683,8 +687,15 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaLaunchCooperativeKernel((const void*)k_binsort, dim3(binsort_ctas), dim3(256), args, 0, s->stream));
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[2], s->stream));
-    k_raster<<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, s->d_lut, thr, s->d_visbuf, s->d_tile_off,
-                                                s->d_sorted, s->d_counters, clear, frame, d_vis, s->d_maxpairs);
+    // vertex heights for the shading pass: the resampled image, the DEM itself when the grid maps onto it one to one,
+    // else (TMA staging off) a gather through the axis table inside the kernel
+    const float* hg = s->d_hgrid ? s->d_hgrid : (s->dem_identity ? s->d_dem : nullptr);
+    const uint32_t hgp = s->d_hgrid ? s->hpitch : s->pitch;
+#define VF_RASTER_LAUNCH(M, D) k_raster<M, D><<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, \
+        s->d_visbuf, s->d_tile_off, s->d_sorted, s->d_counters, clear, frame, d_vis, s->d_maxpairs)
+    if (f.mode == VF_MODE_SHIPPED) { if (f.depth) VF_RASTER_LAUNCH(0, true); else VF_RASTER_LAUNCH(0, false); }
+    else                           { if (f.depth) VF_RASTER_LAUNCH(1, true); else VF_RASTER_LAUNCH(1, false); }
+#undef VF_RASTER_LAUNCH
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());
     return VF_OK;

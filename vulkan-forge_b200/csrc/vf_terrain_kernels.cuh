@@ -95,9 +95,15 @@ __device__ __forceinline__ void vf_prim_vertices(const VfFrame& f, const VfAxis*
 }
 
 // no-depth resolve of a sample as one predicated reduction (no branch around it)
-__device__ __forceinline__ void vf_vis_max_if(bool covered, unsigned long long* key64, uint32_t prim) {
+// (visibility buffer layout: without depth one 32-bit key per pixel, prim + 1, 0 = empty; with depth one 64-bit key,
+// depth bits << 32 | prim, all ones = empty)
+__device__ __forceinline__ void vf_vis_max_if(bool covered, uint32_t* key32, uint32_t prim) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p red.global.max.u32 [%1], %2;\n\t}"
-                 :: "r"((uint32_t)covered), "l"(key64), "r"(prim + 1u) : "memory");      // low word (little endian)
+                 :: "r"((uint32_t)covered), "l"(key32), "r"(prim + 1u) : "memory");
+}
+// key of pixel p in the global visibility buffer, as the pointer vf_vis_update takes
+__device__ __forceinline__ unsigned long long* vf_vis_key(unsigned long long* vis, bool depth, size_t p) {
+    return depth ? vis + p : reinterpret_cast<unsigned long long*>(reinterpret_cast<uint32_t*>(vis) + p);
 }
 // visibility resolve on one sample (global or shared memory)
 __device__ __forceinline__ void vf_vis_update(unsigned long long* key64, bool depth, uint32_t prim, float zf) {
@@ -347,7 +353,7 @@ k_geom(const __grid_constant__ VfFrame f, const __grid_constant__ CUtensorMap de
             zf = vf_depth_at(t, b);
             if (!(zf < 1.0f)) return;
         }
-        vf_vis_update(vis + (size_t)py * f.W + px, depth, prim, zf);
+        vf_vis_update(vf_vis_key(vis, depth, (size_t)py * f.W + px), depth, prim, zf);
     };
     for (uint32_t base = 0; base < n_entries; base += VF_GEOM_THREADS) {
         const uint32_t e = base + tid;
@@ -580,26 +586,100 @@ k_binsort(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, co
 
 // ---------------------------------------------------------------------------------------
 // k_raster: one CTA per 16x16 screen tile, 256 threads.
-//   merge   : the tile's slice of the visibility buffer (written by k_geom's micro path) is
-//             loaded into shared memory and the buffer is reset for the next frame;
-//   coverage: thread k takes the k-th binned primitive of the tile, rebuilds its screen-space
-//             triangle(s) with the same arithmetic as k_bin and resolves in shared memory --
-//             atomicMax(prim+1) (no depth: last drawn wins, src/terrain/pipeline.rs:133) or
-//             atomicMin((depth<<32)|prim) (depth Less);
-//   shading : thread = pixel; rebuilds the winning primitive, perspective-correct varyings,
-//             fragment stage, exact sRGB8; 4 pixels are packed per 16-byte store.
+//   merge   : the tile's slice of the visibility buffer (written by the geometry pass) is loaded and reset for the
+//             next frame; if primitives were binned for this tile (large / clipped ones: rare), they are rebuilt and
+//             resolved in shared memory first (vf_raster_merge, out of line) -- atomicMax(prim+1) (no depth: last
+//             drawn wins, src/terrain/pipeline.rs:133) or atomicMin((depth<<32)|prim) (depth Less);
+//   shading : thread = pixel.  The winning primitive's three vertices come straight from the vertex-height image and
+//             the axis table (no clip machinery, no stack: a winner that does need clipping goes to vf_shade_clipped,
+//             out of line), then perspective-correct varyings -- only the three the shading mode reads --, the fragment
+//             stage, exact sRGB8 from an approximate guess fixed by the threshold table; 4 pixels per 16-byte store.
 #ifndef VF_RASTER_CTAS
-#define VF_RASTER_CTAS 5      // resident CTAs per SM the register budget is set for (4: 0.035 ms, 5: 0.033 ms at c3)
+#define VF_RASTER_CTAS 6      // resident CTAs per SM the register budget is set for (4: 0.031 ms, 6: 0.025 ms, 8: 0.025 ms at c3)
 #endif
+
+static __device__ __noinline__ void
+vf_raster_merge(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+                const uint32_t* __restrict__ sorted_prim, uint32_t beg, uint32_t end, int px0, int py0,
+                unsigned long long* s_key) {
+    const bool depth = f.depth != 0;
+    for (uint32_t k = beg + threadIdx.x; k < end; k += 256) {
+        const uint32_t prim = sorted_prim[k];
+        VfVtx tri[3];
+        vf_prim_vertices(f, axis, dem, prim, tri);
+        vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
+            if (vf_area2(t) >= 0) return;
+            int x0, x1, y0, y1;
+            if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
+            x0 = max(x0, px0); x1 = min(x1, px0 + VF_TILE - 1);
+            y0 = max(y0, py0); y1 = min(y1, py0 + VF_TILE - 1);
+            for (int qy = y0; qy <= y1; ++qy)
+                for (int qx = x0; qx <= x1; ++qx) {
+                    int64_t e[3];
+                    if (!vf_covers(t, qx, qy, e)) continue;
+                    float zf = 0.0f;
+                    if (depth) {
+                        float b[3];
+                        vf_barycentric(e, b);
+                        zf = vf_depth_at(t, b);
+                        if (!(zf < 1.0f)) continue;
+                    }
+                    vf_vis_update(&s_key[(qy - py0) * VF_TILE + (qx - px0)], depth, prim, zf);
+                }
+        });
+    }
+}
+
+// perspective-correct varyings of pixel (px, py) inside screen triangle t, then the fragment stage
+template <int MODE>
+__device__ __forceinline__ uint32_t vf_shade_at(const VfFrame& f, const VfSubTri& t, const int64_t e[3], const float* __restrict__ dem,
+                                                const float4* __restrict__ lut, const float* __restrict__ thr) {
+    float b[3], a[5];
+    vf_barycentric(e, b);
+    const float iw = fmaf(b[2], t.v[2].invw, fmaf(b[1], t.v[1].invw, __fmul_rn(b[0], t.v[0].invw)));
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        // NORTHSTAR reads u, v, h; SHIPPED reads h, x, z (vf_fragment_stage): the others are never computed
+        if ((MODE == 1 && k >= 3) || (MODE == 0 && k < 2)) { a[k] = 0.0f; continue; }
+        const float num = fmaf(b[2], __fmul_rn(t.v[2].a[k], t.v[2].invw),
+                          fmaf(b[1], __fmul_rn(t.v[1].a[k], t.v[1].invw),
+                               __fmul_rn(b[0], __fmul_rn(t.v[0].a[k], t.v[0].invw))));
+        a[k] = __fdiv_rn(num, iw);
+    }
+    return vf_fragment_stage<MODE, true>(f, a, dem, lut, thr);
+}
+
+// the winner needs clipping (a vertex outside near / far / the guard band): the general path, kept out of line
+template <int MODE>
+static __device__ __noinline__ uint32_t
+vf_shade_clipped(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem, const float4* __restrict__ lut,
+                 const float* __restrict__ thr, uint32_t prim, int px, int py, uint32_t clear_rgba) {
+    VfVtx tri[3];
+    vf_prim_vertices(f, axis, dem, prim, tri);
+    uint32_t rgba = clear_rgba;
+    bool done = false;
+    vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
+        if (done || vf_area2(t) >= 0) return;
+        int64_t e[3];
+        if (!vf_covers(t, px, py, e)) return;
+        rgba = vf_shade_at<MODE>(f, t, e, dem, lut, thr);
+        done = true;
+    });
+    return rgba;
+}
+
+// hgrid: the G x G image of vertex heights (vf_terrain.cu: the resampled image, or the DEM itself when the grid maps
+// to it one to one); nullptr: heights are gathered from the DEM through the axis table
+template <int MODE, bool DEPTH>
 __global__ void __launch_bounds__(256, VF_RASTER_CTAS)
 k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
-         const float* __restrict__ dem, const float4* __restrict__ lut,
+         const float* __restrict__ dem, const float* __restrict__ hgrid, uint32_t hpitch, const float4* __restrict__ lut,
          const float* __restrict__ thr_g, unsigned long long* __restrict__ vis,
          const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ sorted_prim,
          const uint32_t* __restrict__ counters, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba,
          uint32_t* __restrict__ out_vis, uint32_t* __restrict__ high_water) {
     __shared__ unsigned long long s_key[VF_TILE * VF_TILE];
-    __shared__ float s_thr[256];
+    __shared__ float s_thr[257];
     const uint32_t tid = threadIdx.x;
     // high_water[2]: most primitives any frame of the batch queued for binning.  The host launches k_binsort
     // speculatively NOT at all while frames queue nothing (vf_terrain.cu); this is how it learns otherwise.
@@ -612,48 +692,29 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
     const bool binned = counters[VF_CNT_PAIRS] != 0u;      // no pairs: k_binsort left tile_off untouched
     const uint32_t beg = binned ? tile_off[tile] : 0u, end = binned ? tile_off[tile + 1] : 0u;
-    const bool depth = f.depth != 0;
-    const unsigned long long empty = depth ? ~0ull : 0ull;
+    const unsigned long long empty = DEPTH ? ~0ull : 0ull;
     const int lx = (int)(tid & 15u), ly = (int)(tid >> 4);
     const int px = px0 + lx, py = py0 + ly;
     const bool inb = px < (int)f.W && py < (int)f.H;
 
     s_thr[tid] = thr_g[tid];
+    if (tid == 0u) s_thr[256] = __int_as_float(0x7f800000);
     unsigned long long key = empty;
-    if (inb) {
-        unsigned long long* g = vis + (size_t)py * f.W + px;
-        key = *g;
-        if (!depth) key &= 0xffffffffull;
-        if (key != empty) *g = empty;                       // self-cleaning: ready for the next frame
+    if (inb) {                                              // self-cleaning: the key is reset for the next frame
+        if (DEPTH) {
+            unsigned long long* g = vis + (size_t)py * f.W + px;
+            key = *g;
+            if (key != empty) *g = empty;
+        } else {
+            uint32_t* g = reinterpret_cast<uint32_t*>(vis) + (size_t)py * f.W + px;
+            key = *g;
+            if (key != 0ull) *g = 0u;
+        }
     }
     if (beg != end) {                                       // block-uniform
         s_key[tid] = key;
         __syncthreads();
-        for (uint32_t k = beg + tid; k < end; k += 256) {
-            const uint32_t prim = sorted_prim[k];
-            VfVtx tri[3];
-            vf_prim_vertices(f, axis, dem, prim, tri);
-            vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
-                if (vf_area2(t) >= 0) return;
-                int x0, x1, y0, y1;
-                if (!vf_subtri_bbox(t, f.W, f.H, x0, x1, y0, y1)) return;
-                x0 = max(x0, px0); x1 = min(x1, px0 + VF_TILE - 1);
-                y0 = max(y0, py0); y1 = min(y1, py0 + VF_TILE - 1);
-                for (int qy = y0; qy <= y1; ++qy)
-                    for (int qx = x0; qx <= x1; ++qx) {
-                        int64_t e[3];
-                        if (!vf_covers(t, qx, qy, e)) continue;
-                        float zf = 0.0f;
-                        if (depth) {
-                            float b[3];
-                            vf_barycentric(e, b);
-                            zf = vf_depth_at(t, b);
-                            if (!(zf < 1.0f)) continue;
-                        }
-                        vf_vis_update(&s_key[(qy - py0) * VF_TILE + (qx - px0)], depth, prim, zf);
-                    }
-            });
-        }
+        vf_raster_merge(f, axis, dem, sorted_prim, beg, end, px0, py0, s_key);
         __syncthreads();
         key = s_key[tid];
     } else {
@@ -661,30 +722,43 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     }
 
     uint32_t id1;
-    if (depth) id1 = key == ~0ull ? 0u : (uint32_t)(key & 0xffffffffull) + 1u;
+    if (DEPTH) id1 = key == ~0ull ? 0u : (uint32_t)(key & 0xffffffffull) + 1u;
     else id1 = (uint32_t)key;
     uint32_t rgba = clear_rgba;
     if (id1 != 0u && inb) {
+        const uint32_t prim = id1 - 1u, cell = prim >> 1, k = prim & 1u, gm = f.G - 1u;
+        uint32_t j = __umulhi(cell, f.gm_inv), i = cell - j * gm;       // j <= cell / gm <= j + 2
+        if (i >= gm) { i -= gm; ++j; }
+        if (i >= gm) { i -= gm; ++j; }
+        // T0 = (a, c, b), T1 = (b, c, d) (src/terrain/mod.rs:575-583): vertex 0 = (i + k, j), 1 = (i, j + 1), 2 = (i + 1, j + k)
+        const float2 ax0 = __ldg(reinterpret_cast<const float2*>(axis + i)), ax1 = __ldg(reinterpret_cast<const float2*>(axis + i + 1u));
+        const float2 az0 = __ldg(reinterpret_cast<const float2*>(axis + j)), az1 = __ldg(reinterpret_cast<const float2*>(axis + j + 1u));
+        float h0, h1, h2;
+        if (hgrid != nullptr) {
+            const float* row0 = hgrid + (size_t)j * hpitch + i;
+            h0 = __ldg(row0 + k); h1 = __ldg(row0 + hpitch); h2 = __ldg(row0 + (k ? hpitch + 1u : 1u));
+        } else {
+            const int tx0 = axis[i].tx, tx1 = axis[i + 1u].tx, ty0 = axis[j].ty, ty1 = axis[j + 1u].ty;
+            h0 = __ldg(dem + (size_t)ty0 * f.dem_pitch + (k ? tx1 : tx0));
+            h1 = __ldg(dem + (size_t)ty1 * f.dem_pitch + tx0);
+            h2 = __ldg(dem + (size_t)(k ? ty1 : ty0) * f.dem_pitch + tx1);
+        }
         VfVtx tri[3];
-        vf_prim_vertices(f, axis, dem, id1 - 1u, tri);
-        bool done = false;
-        vf_for_each_subtri(f, tri, [&](const VfSubTri& t) {
-            if (done || vf_area2(t) >= 0) return;
-            int64_t e[3];
-            if (!vf_covers(t, px, py, e)) return;
-            float b[3], a[5];
-            vf_barycentric(e, b);
-            const float iw = fmaf(b[2], t.v[2].invw, fmaf(b[1], t.v[1].invw, __fmul_rn(b[0], t.v[0].invw)));
+        const float2 axk = k ? ax1 : ax0, azk = k ? az1 : az0;
+        vf_vertex_stage<MODE>(f, axk.x, az0.x, axk.y, az0.y, h0, tri[0]);
+        vf_vertex_stage<MODE>(f, ax0.x, az1.x, ax0.y, az1.y, h1, tri[1]);
+        vf_vertex_stage<MODE>(f, ax1.x, azk.x, ax1.y, azk.y, h2, tri[2]);
+        const uint32_t f0 = vf_clip_flags(tri[0].c), f1 = vf_clip_flags(tri[1].c), f2 = vf_clip_flags(tri[2].c);
+        if (f0 & f1 & f2 & 64u) {                           // every vertex inside near / far / the guard band
+            VfSubTri t;
 #pragma unroll
-            for (int k = 0; k < 5; ++k) {
-                const float num = fmaf(b[2], __fmul_rn(t.v[2].a[k], t.v[2].invw),
-                                  fmaf(b[1], __fmul_rn(t.v[1].a[k], t.v[1].invw),
-                                       __fmul_rn(b[0], __fmul_rn(t.v[0].a[k], t.v[0].invw))));
-                a[k] = __fdiv_rn(num, iw);
-            }
-            rgba = vf_fragment_stage(f, a, dem, lut, s_thr);
-            done = true;
-        });
+            for (int v = 0; v < 3; ++v) vf_to_screen(f, tri[v], t.v[v]);
+            const int32_t sx = px * VF_SUBPIX + VF_HALFPIX, sy = py * VF_SUBPIX + VF_HALFPIX;
+            const int64_t e[3] = {vf_edge(t.v[1], t.v[2], sx, sy), vf_edge(t.v[2], t.v[0], sx, sy), vf_edge(t.v[0], t.v[1], sx, sy)};
+            rgba = vf_shade_at<MODE>(f, t, e, dem, lut, s_thr);
+        } else {
+            rgba = vf_shade_clipped<MODE>(f, axis, dem, lut, s_thr, prim, px, py, clear_rgba);
+        }
     }
     if (out_vis && inb) out_vis[(size_t)py * f.W + px] = id1;
 

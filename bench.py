@@ -277,6 +277,24 @@ def main():
     e2e_s = time.perf_counter() - t0
     barrier()
 
+    # ---- e2e_png: the same steps, frames delivered as .png files in pinned host memory (encoded on the device: only the
+    # compressed bytes cross the bus) ----
+    def png_run(steps):
+        total = 0
+        for _ in range(steps):
+            sc.set_height_from_r32f_async(dem)
+            buf, sizes = sc.render_batch_png_raw(blocks)
+            total += int(sizes.sum()) + int(buf[0, 1])          # device->host result actually read
+        return total
+    png_steps = max(1, args.steps // 4)
+    png_run(2)
+    barrier()
+    t0 = time.perf_counter()
+    png_bytes = png_run(png_steps)
+    torch.cuda.synchronize()
+    png_s = time.perf_counter() - t0
+    barrier()
+
     # ---- parity gate of this very run (outside the timed regions, rank 0): frame 0 of the timed batch against the oracle ----
     parity = None
     if rank == 0:
@@ -295,10 +313,11 @@ def main():
                   "coverage_mismatch": int((gvis != rvis).sum()), "percentile_range_bit_exact": bool(np.float32(hmin) == olo and np.float32(hmax) == ohi),
                   "against": "oracle/ (CPU restatement; pixel parity with the reference's wgpu renderer is unpinned: it cannot run on this box)"}
 
-    t = torch.tensor([dev_ms, e2e_s], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_s, png_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    dev_ms, e2e_s = float(t[0]), float(t[1])
+    dev_ms, e2e_s, png_s = float(t[0]), float(t[1]), float(t[2])
+    png_fps = png_steps * F * world / png_s
     total_frames = args.steps * F * world
     fps = total_frames / (dev_ms / 1e3)
     e2e_fps = total_frames / e2e_s
@@ -330,6 +349,9 @@ def main():
             "mpix_per_s": fps * W * H / 1e6,
             "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": int(dem.nbytes + F * 176), "d2h_bytes_per_step": int(F * W * H * 4),
                     "mpix_per_s": e2e_fps * W * H / 1e6},
+            "e2e_png": {"value": png_fps, "unit": "frames/s", "steps": png_steps, "h2d_bytes_per_step": int(dem.nbytes + F * 176),
+                        "d2h_bytes_per_step": int(png_bytes // png_steps),
+                        "note": "same steps, frames delivered as .png files in pinned host memory, encoded on the device (Scene.render_batch_png_raw)"},
             "gpu_launches": args.steps * F * 2,   # k_geom_march + k_raster per frame (value leg); k_binsort is not launched while frames queue nothing for it
             "parity": parity,
             "roofline": {"bound": "hbm", "limited_by": "instruction issue (see issue)", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_raster"}[dom],

@@ -546,3 +546,23 @@ def test_device_png_batch_equals_rgba_frames(ext, vf, synthetic_dem, tmp_path):
     assert np.array_equal(np.asarray(Image.open(tmp_path / "one.png").convert("RGBA")), want[3])
     with pytest.raises(ValueError):
         sc.render_batch_png(paths[:2], cams)
+
+
+def test_device_png_slots_grow_when_a_file_does_not_fit(ext, vf):
+    """The host slots of a PNG batch start below the worst case; a batch of incompressible frames (a DEM of noise over a
+    fine grid: every pixel a different colour) is repeated with larger slots behind the caller's back."""
+    W, H, G = 512, 512, 1024
+    rng = np.random.default_rng(3)
+    sc = ext.Scene(W, H, grid=G, colormap="terrain")
+    sc.set_height_from_r32f(rng.uniform(-0.05, 0.05, (G, G)).astype(np.float32))
+    sc.set_shading("northstar", depth=True)
+    sc.set_height_range(-0.05, 0.05)
+    cams = [((0.0, 3.0, 0.01), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 60.0, 0.1, 100.0)] * 3      # looking straight down: the frame is full
+    want = np.array(sc.render_batch_rgba(cams))
+    assert (want[0][..., :3] != want[0][0, 0, :3]).any(-1).mean() > 0.3
+    blobs = sc.render_batch_png_bytes(cams)
+    assert len(blobs[0]) > W * H * 4 // 4                   # larger than the first slot size
+    for k, b in enumerate(blobs):
+        assert np.array_equal(_png_decode(b, W, H), want[k])
+    buf, sizes = sc.render_batch_png_raw(cams)
+    assert np.array_equal(_png_decode(bytes(buf[1, :sizes[1]]), W, H), want[1])

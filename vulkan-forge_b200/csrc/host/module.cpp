@@ -39,7 +39,9 @@ namespace pool {
 static std::mutex mu;
 static std::multimap<size_t, void*> free_list;
 static size_t cached_bytes = 0;
-static const size_t kMaxCached = 1ull << 30;
+// pinned blocks kept for reuse (VF_PINNED_POOL_MB, default 4096): batches come back in blocks of hundreds of MB, and
+// cudaHostAlloc / cudaFreeHost of such a block costs tens of milliseconds
+static const size_t kMaxCached = [] { const char* e = std::getenv("VF_PINNED_POOL_MB"); return (size_t)(e ? std::atoll(e) : 4096) << 20; }();
 
 static void* take(size_t bytes) {
     {
@@ -212,6 +214,27 @@ public:
         if (n == 0) throw py::value_error("no cameras given");
         if ((size_t)n != paths.size()) throw py::value_error("need one path per camera");
         png_batch(blocks.data(), n, &paths, nullptr);
+    }
+    // n frames -> (pinned uint8 array (n, cap), uint32 sizes (n,)): file k is buf[k, :sizes[k]]; no copies on the host
+    py::tuple render_batch_png_raw(py::object cameras) {
+        const std::vector<float> blocks = camera_blocks(cameras);
+        const int n = (int)(blocks.size() / 44);
+        if (n == 0) throw py::value_error("no cameras given");
+        py::array_t<uint32_t> sizes(n);
+        uint32_t* sz = sizes.mutable_data();
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            const size_t cap = png_slot_cap();
+            auto buf = pinned_array<uint8_t>({(py::ssize_t)n, (py::ssize_t)cap});
+            uint8_t* p = buf.mutable_data();
+            bool ok;
+            {
+                py::gil_scoped_release nogil;
+                ok = png_render(blocks.data(), n, p, cap, sz);
+            }
+            encode_ms_ = 0.0f;
+            if (ok) return py::make_tuple(buf, sizes);
+        }
+        throw std::runtime_error("PNG batch did not fit its worst-case slots");
     }
     // n frames -> list of bytes objects (each a complete .png file)
     py::list render_batch_png_bytes(py::object cameras) {
@@ -391,16 +414,42 @@ public:
     uint32_t grid() const { return grid_; }
 
 private:
+    // Host slot per file of a PNG batch.  The worst case (vf_png_file_bound, 1.13 x the raw frame) is rarely needed: the
+    // slots start at a quarter of it and follow the largest file seen; a batch that does not fit is repeated with the
+    // bound (png_render), so callers never see the difference.
+    size_t png_slot_cap() const {
+        const size_t bound = (vf_png_file_bound((int)width_, (int)height_) + 255) & ~(size_t)255;
+        const size_t want = png_cap_hint_ ? png_cap_hint_ : std::max<size_t>(bound / 4, 1u << 16);
+        return std::min(bound, (want + 65535) & ~(size_t)65535);
+    }
+    // renders n frames into `p` (n x cap bytes); returns false if a file did not fit (then nothing is valid)
+    bool png_render(const float* blocks, int n, uint8_t* p, size_t cap, uint32_t* sizes) {
+        const size_t bound = (vf_png_file_bound((int)width_, (int)height_) + 255) & ~(size_t)255;
+        const int rc = vf_scene_render_batch_png(scene_, blocks, n, p, cap, sizes);
+        if (rc == VF_E_INVALID && cap < bound && std::string(vf_last_error()).rfind("PNG file", 0) == 0) { png_cap_hint_ = bound; return false; }
+        check(rc);
+        uint32_t mx = 0;
+        for (int k = 0; k < n; ++k) mx = std::max(mx, sizes[k]);
+        png_cap_hint_ = std::max<size_t>(png_cap_hint_ == bound ? 0 : png_cap_hint_, (size_t)mx + mx / 4 + 4096);
+        return true;
+    }
     // render + encode on the device, files into pinned host memory, then to disk and / or bytes objects
     void png_batch(const float* blocks, int n, const std::vector<std::string>* paths, py::list* bytes_out) {
-        const size_t cap = (vf_png_file_bound((int)width_, (int)height_) + 255) & ~(size_t)255;
+        size_t cap = png_slot_cap();
         auto buf = pinned_array<uint8_t>({(py::ssize_t)n, (py::ssize_t)cap});
         std::vector<uint32_t> sizes((size_t)n);
         uint8_t* p = buf.mutable_data();
+        bool ok;
+        { py::gil_scoped_release nogil; ok = png_render(blocks, n, p, cap, sizes.data()); }
+        if (!ok) {                                               // (rare: the retry keeps the GIL)
+            cap = png_slot_cap();
+            buf = pinned_array<uint8_t>({(py::ssize_t)n, (py::ssize_t)cap});
+            p = buf.mutable_data();
+            if (!png_render(blocks, n, p, cap, sizes.data())) throw std::runtime_error("PNG batch did not fit its worst-case slots");
+        }
         std::string io_error;
         {
             py::gil_scoped_release nogil;
-            check(vf_scene_render_batch_png(scene_, blocks, n, p, cap, sizes.data()));
             const auto t0 = std::chrono::steady_clock::now();
             if (paths) {
                 for (int k = 0; k < n && io_error.empty(); ++k) {
@@ -433,6 +482,7 @@ private:
     int mode_ = VF_MODE_SHIPPED;
     bool depth_ = false;
     float encode_ms_ = 0.0f;
+    size_t png_cap_hint_ = 0;
 };
 
 struct Scene : TerrainObject {

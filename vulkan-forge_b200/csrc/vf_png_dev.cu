@@ -3,17 +3,13 @@
 // replaces: image::RgbaImage::save behind Scene / TerrainSpike / Renderer render_png (src/scene/mod.rs:331-333,
 // src/terrain/mod.rs:487-489, src/lib.rs:330-332) for frames that are already on the device.
 //
-//   k_png_encode : one CTA per band of rows.  Sub filter (type 1), then one fixed-Huffman deflate block per band:
-//                  literals, and matches at distance 4 (one pixel) for runs of bytes equal to the byte one pixel back --
-//                  the clear colour, the constant alpha channel, flat shading -- found with per-thread segment scans
-//                  joined by two block scans (last break before / first break after a segment).  Bit lengths are
-//                  prefix-summed and every token ORs its code into the band's bit stream in shared memory.  A band ends
-//                  on a byte boundary (empty stored block, the Z_SYNC_FLUSH idiom), so bands concatenate as bytes.
-//                  Also the band's Adler-32 sums.
-//   k_png_pack   : one CTA per band: the band becomes one IDAT chunk at its final offset (sum of the sizes before it):
-//                  length, type, data (first band: + zlib header, last band: + Adler-32 of the whole stream, folded from
-//                  the per-band sums), CRC-32 computed in parallel (64-byte pieces, each shifted by x^(8 * bytes after it)
-//                  mod P with a table of powers).  CTA 0 adds signature + IHDR, the last CTA IEND and the file size.
+//   k_png_encode : one CTA per band of rows (<= 64 KiB of filtered bytes).  Sub filter (type 1), then one fixed-Huffman
+//                  deflate block per band: literals, and matches at distance 4 (one pixel) for runs of bytes equal to
+//                  the byte one pixel back -- the clear colour, the constant alpha channel, flat shading.  Word-parallel
+//                  analysis, popcount bit counts, one block scan, cyclic emission (vf_png_encode.cuh).  Also the band's
+//                  Adler-32 sums.
+//   k_png_pack   : one CTA per band: the band becomes one IDAT chunk at its final offset, CRC-32 computed in parallel;
+//                  CTA 0 adds signature + IHDR, the last CTA the stream's Adler-32, IEND and the file size (vf_png_pack.cuh).
 // Every IDAT chunk carries its own CRC, so nothing has to be combined on the host; a decoder sees an ordinary PNG.
 #include <string.h>
 
@@ -23,260 +19,7 @@
 #include "vf_internal.h"
 #include "vf_png_dev.h"
 
-#define VF_PNG_THREADS 256
-#define VF_PNG_PIECE 64u                      // CRC piece length in bytes
-#define VF_PNG_POLY 0xEDB88320u
-
-__device__ __forceinline__ uint32_t vf_rev(uint32_t code, uint32_t nbits) { return __brev(code) >> (32u - nbits); }
-
-// fixed Huffman code of a literal byte: (bits, nbits), already reversed for the LSB-first stream (RFC 1951 3.2.6)
-__device__ __forceinline__ uint32_t vf_lit_code(uint32_t v, uint32_t& nbits) {
-    if (v < 144u) { nbits = 8u; return vf_rev(0x30u + v, 8u); }
-    nbits = 9u;
-    return vf_rev(0x190u + (v - 144u), 9u);
-}
-// match of `len` (3..258) at distance 4: length code + extra bits + distance code 3 (5 bits)
-__device__ __forceinline__ uint32_t vf_match_code(uint32_t len, uint32_t& nbits) {
-    const uint16_t base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
-    const uint8_t extra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
-    uint32_t idx = 28u;
-    if (len < 258u) { idx = 0u; while (idx < 27u && base[idx + 1u] <= len) ++idx; }
-    const uint32_t sym = 257u + idx, eb = extra[idx], ev = len - base[idx];
-    uint32_t bits, n;
-    if (sym <= 279u) { n = 7u; bits = vf_rev(sym - 256u, 7u); }
-    else { n = 8u; bits = vf_rev(0xC0u + (sym - 280u), 8u); }
-    bits |= ev << n; n += eb;
-    bits |= vf_rev(3u, 5u) << n; n += 5u;                       // distance 4 -> code 3, no extra bits
-    nbits = n;
-    return bits;
-}
-
-// One band.  Dynamic shared memory: raw bytes | output words | three int arrays of VF_PNG_THREADS.
-__global__ void __launch_bounds__(VF_PNG_THREADS)
-k_png_encode(const uint8_t* __restrict__ frame, uint32_t W, uint32_t H, uint32_t rows_per_band, uint32_t raw_cap, uint32_t out_cap,
-             uint8_t* __restrict__ bands, uint32_t* __restrict__ band_size, uint32_t* __restrict__ band_adler) {
-    extern __shared__ __align__(16) unsigned char png_smem[];
-    uint8_t* raw = png_smem;
-    uint32_t* out = reinterpret_cast<uint32_t*>(png_smem + ((raw_cap + 15u) & ~15u));
-    int* s_a = reinterpret_cast<int*>(out + out_cap / 4u);       // scan scratch
-    int* s_b = s_a + VF_PNG_THREADS;
-    uint32_t* s_c = reinterpret_cast<uint32_t*>(s_b + VF_PNG_THREADS);
-    const uint32_t tid = threadIdx.x, band = blockIdx.x, nbands = gridDim.x;
-    const uint32_t y0 = band * rows_per_band, rows = min(rows_per_band, H - y0);
-    const uint32_t stride = 4u * W + 1u, N = rows * stride;
-
-    // ---- filter: type byte 1 (Sub) + pixel minus the pixel to its left, bytewise ----
-    for (uint32_t w = tid; w < out_cap / 4u; w += VF_PNG_THREADS) out[w] = 0u;
-    const uint32_t* px = reinterpret_cast<const uint32_t*>(frame) + (size_t)y0 * W;
-    for (uint32_t p = tid; p < rows * W; p += VF_PNG_THREADS) {
-        const uint32_t r = p / W, x = p - r * W;
-        const uint32_t cur = __ldg(px + p), prev = x ? __ldg(px + p - 1u) : 0u;
-        const uint32_t d = __vsub4(cur, prev);
-        uint8_t* o = raw + r * stride + 1u + 4u * x;
-        o[0] = (uint8_t)d; o[1] = (uint8_t)(d >> 8); o[2] = (uint8_t)(d >> 16); o[3] = (uint8_t)(d >> 24);
-        if (x == 0u) raw[r * stride] = 1u;
-    }
-    __syncthreads();
-
-    // ---- segments: thread t owns bytes [s0, s1) ----
-    const uint32_t seg = (N + VF_PNG_THREADS - 1u) / VF_PNG_THREADS;
-    const uint32_t s0 = min(tid * seg, N), s1 = min(s0 + seg, N);
-    auto is_match = [&](uint32_t i) -> bool { return i >= 4u && raw[i] == raw[i - 4u]; };
-    int first_break = 0x7fffffff, last_break = -1;              // a break = a byte that does not repeat the byte 4 back
-    uint32_t adler_a = 0u, adler_b = 0u;                        // sum b, sum (N - i) b  (mod 65521 below)
-    for (uint32_t i = s0; i < s1; ++i) {
-        if (!is_match(i)) { if (first_break == 0x7fffffff) first_break = (int)i; last_break = (int)i; }
-        const uint32_t b = raw[i];
-        adler_a += b;
-        adler_b += (N - i) * b;                                  // <= 130 terms below 2^24 each: no overflow within a segment
-    }
-    adler_b %= 65521u;
-    // last break before the segment (prefix max) and first break at or after its end (suffix min)
-    s_a[tid] = last_break; s_b[tid] = first_break;
-    __syncthreads();
-    for (uint32_t d = 1u; d < VF_PNG_THREADS; d <<= 1) {
-        const int pa = tid >= d ? s_a[tid - d] : -1, pb = tid + d < VF_PNG_THREADS ? s_b[tid + d] : 0x7fffffff;
-        __syncthreads();
-        s_a[tid] = max(s_a[tid], pa); s_b[tid] = min(s_b[tid], pb);
-        __syncthreads();
-    }
-    const int prev_break = tid ? s_a[tid - 1u] : -1;                                   // inclusive scans, shifted by one
-    const int next_break = tid + 1u < VF_PNG_THREADS ? min(s_b[tid + 1u], (int)N) : (int)N;
-    __syncthreads();
-
-    // Token of byte i, given the run [start, end) of matching bytes it lies in: runs shorter than 3 are literals, longer
-    // ones are cut into matches of 258 (a tail shorter than 3 is literals again).  Returns the code and its length
-    // (0 bits: the byte is inside a match that an earlier byte emitted).
-    auto token = [&](uint32_t i, int start, int end, uint32_t& nbits) -> uint32_t {
-        const uint32_t L = (uint32_t)(end - start), p = i - (uint32_t)start;
-        if (L >= 3u) {
-            const uint32_t c = p / 258u, o = p - c * 258u, cl = min(258u, L - c * 258u);
-            if (cl >= 3u) {
-                if (o != 0u) { nbits = 0u; return 0u; }
-                return vf_match_code(cl, nbits);
-            }
-        }
-        return vf_lit_code(raw[i], nbits);
-    };
-    // walk the segment once per pass; `emit` receives (code, nbits) of every byte
-    auto walk = [&](auto&& emit) {
-        int brk = prev_break;                                    // last break seen so far
-        int run_end = -1;                                        // end of the run that contains the current byte (when inside one)
-        for (uint32_t i = s0; i < s1; ++i) {
-            uint32_t nbits;
-            uint32_t code;
-            if (!is_match(i)) {
-                brk = (int)i;
-                code = vf_lit_code(raw[i], nbits);
-            } else {
-                if (run_end <= (int)i) {                         // entering a run (or the segment starts inside one)
-                    uint32_t j = i + 1u;
-                    while (j < s1 && is_match(j)) ++j;
-                    run_end = j < s1 ? (int)j : next_break;
-                }
-                code = token(i, brk + 1, run_end, nbits);
-            }
-            emit(code, nbits);
-        }
-    };
-    uint32_t my_bits = 0u;
-    walk([&](uint32_t, uint32_t nbits) { my_bits += nbits; });
-
-    // ---- exclusive prefix sum of the bit counts (+ 3 header bits), Adler reduction ----
-    s_c[tid] = my_bits;
-    s_a[tid] = (int)(adler_a % 65521u); s_b[tid] = (int)adler_b;
-    __syncthreads();
-    for (uint32_t d = 1u; d < VF_PNG_THREADS; d <<= 1) {
-        const uint32_t pc = tid >= d ? s_c[tid - d] : 0u;
-        const int pa = tid >= d ? s_a[tid - d] : 0, pb = tid >= d ? s_b[tid - d] : 0;
-        __syncthreads();
-        s_c[tid] += pc; s_a[tid] = (s_a[tid] + pa) % 65521; s_b[tid] = (s_b[tid] + pb) % 65521;
-        __syncthreads();
-    }
-    const bool last_band = band + 1u == nbands;
-    uint32_t bitpos = 3u + s_c[tid] - my_bits;
-    const uint32_t total_bits = 3u + s_c[VF_PNG_THREADS - 1u];
-    if (tid == 0u) out[0] = (last_band ? 1u : 0u) | (1u << 1);   // BFINAL, BTYPE = 01 (fixed Huffman)
-    __syncthreads();
-    walk([&](uint32_t code, uint32_t nbits) {
-        if (nbits == 0u) return;
-        const uint32_t w = bitpos >> 5, off = bitpos & 31u;
-        atomicOr(&out[w], code << off);
-        if (off + nbits > 32u) atomicOr(&out[w + 1u], code >> (32u - off));
-        bitpos += nbits;
-    });
-    __syncthreads();
-    // end of block (code 256: seven zero bits), then the byte boundary
-    uint32_t end_bits = total_bits + 7u;
-    uint32_t nbytes;
-    if (last_band) {
-        nbytes = (end_bits + 7u) >> 3;
-    } else {                                                     // empty stored block: 000, pad, 00 00 FF FF
-        end_bits += 3u;
-        nbytes = (end_bits + 7u) >> 3;
-        if (tid == 0u) {
-            uint8_t* ob = reinterpret_cast<uint8_t*>(out);
-            ob[nbytes] = 0x00; ob[nbytes + 1u] = 0x00; ob[nbytes + 2u] = 0xff; ob[nbytes + 3u] = 0xff;
-        }
-        nbytes += 4u;
-    }
-    __syncthreads();
-    uint8_t* dst = bands + (size_t)band * out_cap;
-    for (uint32_t w = tid; w < (nbytes + 3u) / 4u; w += VF_PNG_THREADS) reinterpret_cast<uint32_t*>(dst)[w] = out[w];
-    if (tid == 0u) {
-        band_size[band] = nbytes;
-        band_adler[3u * band] = (uint32_t)s_a[VF_PNG_THREADS - 1u];       // sum of bytes mod 65521
-        band_adler[3u * band + 1u] = (uint32_t)s_b[VF_PNG_THREADS - 1u];  // sum (N - i) b_i mod 65521
-        band_adler[3u * band + 2u] = N;
-    }
-}
-
-// a * b mod P in the reflected representation (x^0 is bit 31), as zlib's multmodp
-__device__ __forceinline__ uint32_t vf_gf_mul(uint32_t a, uint32_t b) {
-    uint32_t p = 0u;
-    for (uint32_t m = 1u << 31; m; m >>= 1) {
-        if (a & m) p ^= b;
-        b = (b & 1u) ? (b >> 1) ^ VF_PNG_POLY : b >> 1;
-    }
-    return p;
-}
-
-// pow_piece[j] = x^(8 * VF_PNG_PIECE * j) mod P, pow_byte[r] = x^(8 r) mod P (r < VF_PNG_PIECE)
-__global__ void __launch_bounds__(VF_PNG_THREADS)
-k_png_pack(const uint8_t* __restrict__ bands, uint32_t out_cap, const uint32_t* __restrict__ band_size,
-           const uint32_t* __restrict__ band_adler, const uint8_t* __restrict__ preamble /* 33 bytes */,
-           const uint32_t* __restrict__ pow_piece, const uint32_t* __restrict__ pow_byte,
-           uint8_t* __restrict__ file, uint32_t file_cap, uint32_t* __restrict__ file_size) {
-    extern __shared__ __align__(16) unsigned char png_smem[];
-    uint8_t* chunk = png_smem;                                   // 'IDAT' + data
-    __shared__ uint32_t s_tab[256];
-    __shared__ uint32_t s_red[VF_PNG_THREADS];
-    __shared__ uint32_t s_adler;
-    const uint32_t tid = threadIdx.x, band = blockIdx.x, nbands = gridDim.x;
-    const bool first = band == 0u, last = band + 1u == nbands;
-    {   // byte-wise CRC table
-        uint32_t c = tid;
-        for (int k = 0; k < 8; ++k) c = (c & 1u) ? (c >> 1) ^ VF_PNG_POLY : c >> 1;
-        s_tab[tid] = c;
-    }
-    // offset of this chunk: preamble + every chunk before it (12 bytes of framing each; the first holds the zlib header)
-    uint32_t part = 0u;
-    for (uint32_t k = tid; k < band; k += VF_PNG_THREADS) part += band_size[k] + 12u;
-    s_red[tid] = part;
-    __syncthreads();
-    for (uint32_t d = VF_PNG_THREADS / 2u; d; d >>= 1) { if (tid < d) s_red[tid] += s_red[tid + d]; __syncthreads(); }
-    const uint32_t offset = 33u + s_red[0] + (band ? 2u : 0u);
-    __syncthreads();
-    if (last && tid == 0u) {                                     // Adler-32 of the whole filtered stream from the per-band sums
-        uint32_t A = 1u, B = 0u;
-        for (uint32_t k = 0u; k < nbands; ++k) {
-            const uint32_t a = band_adler[3u * k], b = band_adler[3u * k + 1u], n = band_adler[3u * k + 2u];
-            // over a band of n bytes: B += n * A_before + sum (n - i) b_i ; A += sum b_i
-            B = (uint32_t)((B + (unsigned long long)(n % 65521u) * A + b) % 65521u);
-            A = (A + a) % 65521u;
-        }
-        s_adler = (B << 16) | A;
-    }
-    const uint32_t bsz = band_size[band];
-    const uint32_t dl = bsz + (first ? 2u : 0u) + (last ? 4u : 0u);        // chunk data length
-    const uint32_t n = 4u + dl;                                  // bytes under the CRC
-    if (tid == 0u) { chunk[0] = 'I'; chunk[1] = 'D'; chunk[2] = 'A'; chunk[3] = 'T'; if (first) { chunk[4] = 0x78; chunk[5] = 0x01; } }
-    const uint8_t* src = bands + (size_t)band * out_cap;
-    uint8_t* body = chunk + 4u + (first ? 2u : 0u);
-    for (uint32_t k = tid; k < bsz; k += VF_PNG_THREADS) body[k] = src[k];
-    __syncthreads();
-    if (last && tid == 0u) { const uint32_t a = s_adler; body[bsz] = (uint8_t)(a >> 24); body[bsz + 1u] = (uint8_t)(a >> 16); body[bsz + 2u] = (uint8_t)(a >> 8); body[bsz + 3u] = (uint8_t)a; }
-    __syncthreads();
-    // CRC-32: pieces counted from the END (piece j ends VF_PNG_PIECE * j bytes before the end), each run from a zero
-    // register and multiplied by x^(8 * bytes after it); the initial all-ones register is shifted by the whole length
-    uint32_t acc = 0u;
-    const uint32_t npieces = (n + VF_PNG_PIECE - 1u) / VF_PNG_PIECE;
-    for (uint32_t j = tid; j < npieces; j += VF_PNG_THREADS) {
-        const uint32_t e = n - j * VF_PNG_PIECE, b = e > VF_PNG_PIECE ? e - VF_PNG_PIECE : 0u;
-        uint32_t c = 0u;
-        for (uint32_t k = b; k < e; ++k) c = s_tab[(c ^ chunk[k]) & 255u] ^ (c >> 8);
-        acc ^= j ? vf_gf_mul(pow_piece[j], c) : c;
-    }
-    if (tid == 0u) acc ^= vf_gf_mul(vf_gf_mul(pow_piece[n / VF_PNG_PIECE], pow_byte[n % VF_PNG_PIECE]), 0xffffffffu);
-    s_red[tid] = acc;
-    __syncthreads();
-    for (uint32_t d = VF_PNG_THREADS / 2u; d; d >>= 1) { if (tid < d) s_red[tid] ^= s_red[tid + d]; __syncthreads(); }
-    const uint32_t crc = s_red[0] ^ 0xffffffffu;
-    // ---- write: [len][IDAT + data][crc] at `offset` ----
-    const bool fits = offset + 12u + dl + (last ? 12u : 0u) <= file_cap;
-    if (fits) {
-        uint8_t* o = file + offset;
-        if (tid == 0u) { o[0] = (uint8_t)(dl >> 24); o[1] = (uint8_t)(dl >> 16); o[2] = (uint8_t)(dl >> 8); o[3] = (uint8_t)dl; }
-        for (uint32_t k = tid; k < n; k += VF_PNG_THREADS) o[4u + k] = chunk[k];
-        if (tid == 0u) { uint8_t* c4 = o + 4u + n; c4[0] = (uint8_t)(crc >> 24); c4[1] = (uint8_t)(crc >> 16); c4[2] = (uint8_t)(crc >> 8); c4[3] = (uint8_t)crc; }
-        if (first) for (uint32_t k = tid; k < 33u; k += VF_PNG_THREADS) file[k] = preamble[k];
-        if (last && tid < 12u) {
-            const uint8_t iend[12] = {0, 0, 0, 0, 'I', 'E', 'N', 'D', 0xae, 0x42, 0x60, 0x82};
-            o[8u + n + tid] = iend[tid];
-        }
-    }
-    if (last && tid == 0u) *file_size = fits ? offset + 12u + dl + 12u : 0xffffffffu;     // all ones: did not fit
-}
+#include "vf_png_kernels.cuh"     // k_png_encode, k_png_pack
 
 // ---------------------------------------------------------------------------------------------------------------
 static uint32_t host_gf_mul(uint32_t a, uint32_t b) {
@@ -305,6 +48,8 @@ size_t vf_png_dev_bound(int w, int h) {
 }
 
 int vf_png_dev_create(int w, int h, int slots, VfPngDev** out) {
+    // a band is at least one row, and a thread's segment of it must fit VF_PNG_SEG_WORDS words: rows up to 8192 pixels
+    if (w <= 0 || h <= 0 || w > 8192) return vf_set_error(VF_E_INVALID, "PNG encoder: width must be in 1..8192");
     VfPngDev* e = new VfPngDev();
     e->W = (uint32_t)w; e->H = (uint32_t)h;
     const size_t stride = (size_t)w * 4 + 1;
@@ -312,10 +57,10 @@ int vf_png_dev_create(int w, int h, int slots, VfPngDev** out) {
     e->nbands = ((uint32_t)h + e->rows_per_band - 1) / e->rows_per_band;
     e->raw_cap = (uint32_t)((e->rows_per_band * stride + 15) & ~(size_t)15);
     e->band_cap = (uint32_t)(((e->rows_per_band * stride * 9 + 7) / 8 + 64 + 15) & ~(size_t)15);
-    e->file_cap = (uint32_t)vf_png_dev_bound(w, h);
+    e->file_cap = (uint32_t)((vf_png_dev_bound(w, h) + 255) & ~(size_t)255);
     e->slots = slots;
-    e->smem_encode = e->raw_cap + e->band_cap + 3 * VF_PNG_THREADS * 4 + 16;
-    e->smem_pack = e->band_cap + 32;
+    e->smem_encode = (size_t)e->raw_cap + e->band_cap + e->raw_cap + 64;      // raw | out | meta + woff (2 + 2 bytes per word)
+    e->smem_pack = e->band_cap + 96;
     auto fail = [&](const char* what, cudaError_t err) {
         vf_png_dev_destroy(e);
         (void)cudaGetLastError();
@@ -380,7 +125,7 @@ int vf_png_dev_encode(VfPngDev* e, const uint8_t* d_frame, int slot, cudaStream_
 
 // Any host RGBA8 image -> .png bytes through the device encoder (the triangle path's render_png, tests).
 extern "C" int vf_png_encode_rgba(const uint8_t* rgba_host, int w, int h, uint8_t* out_host, size_t cap, uint32_t* size) {
-    if (!rgba_host || !out_host || !size || w <= 0 || h <= 0 || w > 16384 || h > 16384) return vf_set_error(VF_E_INVALID, "invalid PNG arguments");
+    if (!rgba_host || !out_host || !size || w <= 0 || h <= 0 || w > 8192 || h > 65535) return vf_set_error(VF_E_INVALID, "invalid PNG arguments (width <= 8192)");
     int rc = vf_require_device();
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(vf_util_mutex());

@@ -871,7 +871,10 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
     if (rc) return rc;
     for (int attempt = 0; attempt < 8; ++attempt) {
         rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending, s->marks, png_out);
-        if (rc) return rc;
+        if (rc) {                                            // nothing of the failed call may still be in flight when the caller reacts
+            cudaStreamSynchronize(s->stream); cudaStreamSynchronize(s->copy_stream);
+            return rc;
+        }
         VF_CUDA(cudaStreamSynchronize(s->stream));
         if (out_host || png_out) VF_CUDA(cudaStreamSynchronize(s->copy_stream));
         scene_finish_metrics(s, s->marks);

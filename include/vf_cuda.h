@@ -112,6 +112,15 @@ int vf_dem_normalize(float *data, size_t n, int mode, float eps, float lo, float
 int vf_dem_ingest_f64(const double *src, size_t n, float scale, float *dst);
 int vf_dem_ingest_f32(const float *src, size_t n, float scale, float *dst);
 
+/* Allocation-free variant of vf_dem_minmax.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  d_data: n floats in DEVICE memory of the current device; d_out2: two floats (lo, hi) in device memory;
+ * the kernels are enqueued on cuda_stream (a cudaStream_t, NULL = the legacy stream) and the call returns without
+ * waiting.  Nothing is allocated: the scratch (accumulators + the <= 131 071 strided samples of clamp = 1) is one
+ * static device array of 512.25 KiB inside the library, held by every GPU that loads it.  n > 4 294 967 295 is rejected
+ * with VF_E_INVALID.  All calls share that array: calls that overlap on the GPU race -- serialise them (one stream). */
+int vf_dem_minmax_noalloc_async(const float *d_data, size_t n, int clamp, float *d_out2, void *cuda_stream);
+
 /* ---- device-resident height images ----------------------------------------------------------
  * replaces: the Vec<f32> that Renderer.add_terrain keeps on the host (src/lib.rs:351-418) and everything computed
  * from it (terrain_stats :424-429, normalize_terrain :478-493, upload_height_r32f :496-571).  The array crosses

@@ -531,3 +531,84 @@ extern "C" int vf_dem_ingest_f32(const float* src, size_t n, float scale, float*
     vf_height_destroy(t);
     return rc;
 }
+
+// ---- allocation-free variant (no counterpart in the reference) ----------
+// vf_dem_minmax for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): input and output are DEVICE pointers, the work is enqueued on the caller's stream, and the scratch the
+// kernels need -- the accumulator block of k_dem_moments and the gathered sample of k_dem_gather / k_dem_select -- lives
+// in ONE file-scope device array of fixed size: 256 B + 131 072 floats = 512.25 KiB, held by every GPU that loads the
+// library until the process exits.  The sample of terrain_stats.rs:23-27 never exceeds 131 071 values (n in (65536,
+// 131072) has step 1), so the array bounds the sample for every n the gather can index (n <= 2^32 - 1).
+// Every call shares the array and finds the previous call's contents in it: the accumulators are re-initialised by the
+// first kernel of each call, the sample is overwritten up to the m values the call reads.  Calls that overlap on the GPU
+// (two streams, two host threads) race on the array: serialise them.
+#define VF_NOALLOC_MAX_SAMPLES 131072u
+#define VF_NOALLOC_MAX_N 0xffffffffull
+struct VfNoAllocScratch {
+    Moments m;                                            // 48 bytes
+    unsigned char pad[256 - sizeof(Moments)];
+    float vals[VF_NOALLOC_MAX_SAMPLES];
+};
+static __device__ __align__(256) VfNoAllocScratch g_noalloc_scratch;
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for once
+// per device, with that device current, and cached.
+static VfNoAllocScratch* g_noalloc_ptr[64] = {nullptr};
+static std::mutex g_noalloc_mu;
+static int noalloc_scratch(VfNoAllocScratch** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) { (void)cudaGetLastError(); return vf_set_error(VF_E_NO_DEVICE, "No suitable GPU adapter (no current CUDA device)"); }
+    if (dev >= 64) return vf_set_error(VF_E_INVALID, "device %d: at most 64 devices are supported", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) { (void)cudaGetLastError(); return vf_set_error(VF_E_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e)); }
+        g_noalloc_ptr[dev] = static_cast<VfNoAllocScratch*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return VF_OK;
+}
+
+__global__ void k_noalloc_begin(Moments* m) {            // what must not carry over from the previous call
+    m->acc[0] = 0xffffffffu; m->acc[1] = 0u; m->acc[2] = 0u; m->acc[3] = 0u;
+    m->accd[0] = 0.0; m->accd[1] = 0.0;
+    m->first = ~0ull;
+    m->out2[0] = 0.0f; m->out2[1] = 0.0f;
+}
+// (lo, hi) from the accumulators; a zero extreme takes the sign of the first zero of the array (as fix-up of stats_device)
+__global__ void k_noalloc_finish(const float* __restrict__ data, const Moments* __restrict__ m, float* __restrict__ out2) {
+    float lo = vf_key_float(m->acc[0]), hi = vf_key_float(m->acc[1]);
+    if (m->first != ~0ull) {
+        const float z = data[m->first];
+        if (lo == 0.0f) lo = z;
+        if (hi == 0.0f) hi = z;
+    }
+    out2[0] = lo; out2[1] = hi;
+}
+
+extern "C" int vf_dem_minmax_noalloc_async(const float* d_data, size_t n, int clamp, float* d_out2, void* cuda_stream) {
+    if (!d_data || !d_out2) return vf_set_error(VF_E_INVALID, "null argument");
+    if (n == 0) return vf_set_error(VF_E_INVALID, "heightmap slice empty");
+    if ((unsigned long long)n > VF_NOALLOC_MAX_N)
+        return vf_set_error(VF_E_INVALID, "vf_dem_minmax_noalloc_async: n = %zu exceeds the maximum of %llu values", n, VF_NOALLOC_MAX_N);
+    VfNoAllocScratch* sc = nullptr;
+    const int rc = noalloc_scratch(&sc);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (!clamp) {
+        k_noalloc_begin<<<1, 1, 0, st>>>(&sc->m);
+        k_dem_moments<<<grid_for(n, 256), 256, 0, st>>>(d_data, (uint32_t)n, 1u, (uint32_t)n, 0ull, 0.0f, sc->m.acc, sc->m.accd, &sc->m.first);
+        k_noalloc_finish<<<1, 1, 0, st>>>(d_data, &sc->m, d_out2);
+    } else {
+        size_t step, m;
+        sample_plan(n, step, m);
+        if (m > VF_NOALLOC_MAX_SAMPLES)
+            return vf_set_error(VF_E_INVALID, "vf_dem_minmax_noalloc_async: sample of %zu values exceeds the scratch array (%u)", m, VF_NOALLOC_MAX_SAMPLES);
+        const uint32_t r1 = (uint32_t)((float)m * 0.01f), r99 = (uint32_t)((float)m * 0.99f);      // terrain_stats.rs:32-33
+        k_dem_gather<<<grid_for(m, 256), 256, 0, st>>>(d_data, (uint32_t)n, (uint32_t)n, step, (uint32_t)m, sc->vals);
+        k_dem_select<<<1, 1024, 0, st>>>(sc->vals, (uint32_t)m, r1, r99, d_out2);
+    }
+    VF_CUDA(cudaGetLastError());
+    return VF_OK;
+}

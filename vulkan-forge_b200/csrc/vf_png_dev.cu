@@ -11,6 +11,7 @@
 //   k_png_pack   : one CTA per band: the band becomes one IDAT chunk at its final offset, CRC-32 computed in parallel;
 //                  CTA 0 adds signature + IHDR, the last CTA the stream's Adler-32, IEND and the file size (vf_png_pack.cuh).
 // Every IDAT chunk carries its own CRC, so nothing has to be combined on the host; a decoder sees an ordinary PNG.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -39,9 +40,14 @@ static uint32_t host_crc(const uint8_t* p, size_t n) {
     return c ^ 0xffffffffu;
 }
 
+// filtered bytes a band aims for (a band is whole rows, at least one): VF_PNG_BAND_BYTES for tuning runs
+static size_t band_target() {
+    static const size_t v = [] { const char* e = getenv("VF_PNG_BAND_BYTES"); const long x = e ? atol(e) : 0; return (size_t)(x >= 1024 && x <= 32768 ? x : 32768); }();
+    return v;
+}
 size_t vf_png_dev_bound(int w, int h) {
     const size_t stride = (size_t)w * 4 + 1;
-    const uint32_t rpb = (uint32_t)std::max<size_t>(1, 32768 / stride);
+    const uint32_t rpb = (uint32_t)std::max<size_t>(1, band_target() / stride);
     const size_t nb = ((size_t)h + rpb - 1) / rpb;
     const size_t band_cap = ((rpb * stride * 9 + 7) / 8 + 64 + 15) & ~(size_t)15;
     return 33 + nb * (band_cap + 12) + 2 + 4 + 12 + 64;
@@ -53,7 +59,7 @@ int vf_png_dev_create(int w, int h, int slots, VfPngDev** out) {
     VfPngDev* e = new VfPngDev();
     e->W = (uint32_t)w; e->H = (uint32_t)h;
     const size_t stride = (size_t)w * 4 + 1;
-    e->rows_per_band = (uint32_t)std::max<size_t>(1, 32768 / stride);
+    e->rows_per_band = (uint32_t)std::max<size_t>(1, band_target() / stride);
     e->nbands = ((uint32_t)h + e->rows_per_band - 1) / e->rows_per_band;
     e->raw_cap = (uint32_t)((e->rows_per_band * stride + 15) & ~(size_t)15);
     e->band_cap = (uint32_t)(((e->rows_per_band * stride * 9 + 7) / 8 + 64 + 15) & ~(size_t)15);

@@ -228,7 +228,8 @@ __device__ __noinline__ uint32_t vf_gm_drain_cells(const VfFrame& f, VfGmWarpT<D
                 const VfSVtx& a = t.v[(i + 1) % 3];
                 const VfSVtx& b = t.v[(i + 2) % 3];
                 A[i] = b.Y - a.Y; B[i] = a.X - b.X;
-                const bool tl = vf_top_left(a, b);
+                // vf_top_left(a, b) on the differences (|X|, |Y| < 2^23: they cannot wrap): b.Y > a.Y, or level and b.X < a.X
+                const bool tl = (A[i] > 0) | ((A[i] == 0) & (B[i] > 0));
                 nbias |= tl ? 0u : (1u << i);
                 E[i] = (int32_t)((uint32_t)A[i] * (uint32_t)(sx - a.X) + (uint32_t)B[i] * (uint32_t)(sy - a.Y)) - (tl ? 0 : 1);
             }

@@ -687,39 +687,49 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
         const uint32_t nbig = counters[VF_CNT_BIG];
         if (nbig) atomicMax(&high_water[2], nbig);
     }
-    const uint32_t tyi = blockIdx.y, txi = blockIdx.x;      // grid = tiles_x x tiles_y
-    const uint32_t tile = tyi * f.tiles_x + txi;
-    const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
-    const bool binned = counters[VF_CNT_PAIRS] != 0u;      // no pairs: k_binsort left tile_off untouched
-    const uint32_t beg = binned ? tile_off[tile] : 0u, end = binned ? tile_off[tile + 1] : 0u;
-    const unsigned long long empty = DEPTH ? ~0ull : 0ull;
-    const int lx = (int)(tid & 15u), ly = (int)(tid >> 4);
-    const int px = px0 + lx, py = py0 + ly;
-    const bool inb = px < (int)f.W && py < (int)f.H;
-
-    s_thr[tid] = thr_g[tid];
-    if (tid == 0u) s_thr[256] = __int_as_float(0x7f800000);
-    unsigned long long key = empty;
-    if (inb) {                                              // self-cleaning: the key is reset for the next frame
-        if (DEPTH) {
-            unsigned long long* g = vis + (size_t)py * f.W + px;
-            key = *g;
-            if (key != empty) *g = empty;
+    unsigned long long key;
+    {
+        const uint32_t tyi = blockIdx.y, txi = blockIdx.x;  // grid = tiles_x x tiles_y
+        const uint32_t tile = tyi * f.tiles_x + txi;
+        const int px0 = (int)txi * VF_TILE, py0 = (int)tyi * VF_TILE;
+        const bool binned = counters[VF_CNT_PAIRS] != 0u;  // no pairs: k_binsort left tile_off untouched
+        const uint32_t beg = binned ? tile_off[tile] : 0u, end = binned ? tile_off[tile + 1] : 0u;
+        const unsigned long long empty = DEPTH ? ~0ull : 0ull;
+        const int px = px0 + (int)(tid & 15u), py = py0 + (int)(tid >> 4);
+        s_thr[tid] = thr_g[tid];
+        if (tid == 0u) s_thr[256] = __int_as_float(0x7f800000);
+        key = empty;
+        if (px < (int)f.W && py < (int)f.H) {               // self-cleaning: the key is reset for the next frame
+            if (DEPTH) {
+                unsigned long long* g = vis + (size_t)py * f.W + px;
+                key = *g;
+                if (key != empty) *g = empty;
+            } else {
+                uint32_t* g = reinterpret_cast<uint32_t*>(vis) + (size_t)py * f.W + px;
+                key = *g;
+                if (key != 0ull) *g = 0u;
+            }
+        }
+        if (beg != end) {                                   // block-uniform, rare
+            s_key[tid] = key;
+            __syncthreads();
+            vf_raster_merge(f, axis, dem, sorted_prim, beg, end, px0, py0, s_key);
+            __syncthreads();
+            uint32_t t2;                                    // (nothing but the key's address is needed after the call, and it is
+            asm volatile("mov.u32 %0, %%tid.x;" : "=r"(t2));   // re-derived: no register has to survive the call)
+            key = s_key[t2];
         } else {
-            uint32_t* g = reinterpret_cast<uint32_t*>(vis) + (size_t)py * f.W + px;
-            key = *g;
-            if (key != 0ull) *g = 0u;
+            __syncthreads();                                // s_thr
         }
     }
-    if (beg != end) {                                       // block-uniform
-        s_key[tid] = key;
-        __syncthreads();
-        vf_raster_merge(f, axis, dem, sorted_prim, beg, end, px0, py0, s_key);
-        __syncthreads();
-        key = s_key[tid];
-    } else {
-        __syncthreads();                                    // s_thr
-    }
+    // Thread and tile indices are read again here (volatile: not merged with the reads above), so that the values
+    // above die before the out-of-line call instead of being spilled around it on every path.
+    uint32_t tid_b, ctax, ctay;
+    asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid_b));
+    asm volatile("mov.u32 %0, %%ctaid.x;" : "=r"(ctax));
+    asm volatile("mov.u32 %0, %%ctaid.y;" : "=r"(ctay));
+    const int px = (int)(ctax * VF_TILE + (tid_b & 15u)), py = (int)(ctay * VF_TILE + (tid_b >> 4));
+    const bool inb = px < (int)f.W && py < (int)f.H;
 
     uint32_t id1;
     if (DEPTH) id1 = key == ~0ull ? 0u : (uint32_t)(key & 0xffffffffull) + 1u;
@@ -767,7 +777,7 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     const uint32_t r2 = __shfl_down_sync(0xffffffffu, rgba, 2);
     const uint32_t r3 = __shfl_down_sync(0xffffffffu, rgba, 3);
     if ((f.W & 3u) == 0u) {
-        if ((tid & 3u) == 0u && inb)
+        if ((tid_b & 3u) == 0u && inb)
             *reinterpret_cast<uint4*>(out_rgba + ((size_t)py * f.W + px) * 4) = make_uint4(rgba, r1, r2, r3);
     } else if (inb) {
         *reinterpret_cast<uint32_t*>(out_rgba + ((size_t)py * f.W + px) * 4) = rgba;

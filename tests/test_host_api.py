@@ -191,3 +191,38 @@ def test_product_package_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp", ".inc")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "vf_oracle" not in text and "libvfo" not in text and "vfo_" not in text, f
+
+
+def test_integration_doc_matches_header():
+    """INTEGRATION.md's Rust block binds exactly the functions include/vf_cuda.h declares, and its #[repr(C)] structs
+    have the header's fields in the header's order with matching types (a host built from the document must not read a
+    timing shifted by four bytes)."""
+    import re
+    hdr = open(os.path.join(ROOT, "include", "vf_cuda.h")).read()
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    rust = doc[doc.index("```rust"):doc.index("```\n", doc.index("```rust") + 8)]
+    declared = set(re.findall(r"^(?:int|void|size_t|const char \*)\s*\*?(vf_\w+)\(", hdr, re.M))
+    bound = set(re.findall(r"pub fn (vf_\w+)\(", rust))
+    assert declared == bound, (sorted(declared - bound), sorted(bound - declared))
+    ctype = {"uint32_t": "u32", "uint64_t": "u64", "int": "i32", "float": "f32", "char": "c_char"}
+
+    def c_fields(name):
+        body = re.search(r"typedef struct \{([^{}]*)\}\s*" + name + ";", hdr).group(1)
+        body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+        out = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if not decl:
+                continue
+            ty, rest = decl.split(None, 1)
+            for item in rest.split(","):
+                m = re.match(r"\s*(\w+)(?:\[(\d+)\])?\s*$", item)
+                out.append((m.group(1), ctype[ty] if not m.group(2) else f"[{ctype[ty]}; {m.group(2)}]"))
+        return out
+
+    def rust_fields(name):
+        body = re.search(r"pub struct " + name + r" \{(.*?)\}", rust, re.S).group(1)
+        return [(m.group(1), m.group(2).strip()) for m in re.finditer(r"pub (\w+): ([^,}]+)", body)]
+
+    for c_name, r_name in (("vf_device_info_t", "VfDeviceInfo"), ("vf_frame_stats_t", "VfFrameStats"), ("vf_render_metrics_t", "VfRenderMetrics")):
+        assert c_fields(c_name) == rust_fields(r_name), (c_name, c_fields(c_name), rust_fields(r_name))

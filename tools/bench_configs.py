@@ -91,8 +91,28 @@ for n, d in (("4096^2", dem4096),):
     ext.dem_minmax(d, True)
     t0 = time.perf_counter(); g = ext.dem_minmax(d, True); tg = time.perf_counter() - t0
     t0 = time.perf_counter(); r = o.min_max(d, True); tc = time.perf_counter() - t0
-    emit(config=f"min_max(clamp=true) {n}", gpu_ms=tg * 1e3, cpu_ms=tc * 1e3, equal=bool(np.float32(g[0]) == r[0] and np.float32(g[1]) == r[1]),
-         note="GPU time includes the 64 MiB H2D of a host array")
+    emit(config=f"min_max(clamp=true) {n} host array", gpu_ms=tg * 1e3, cpu_ms=tc * 1e3, equal=bool(np.float32(g[0]) == r[0] and np.float32(g[1]) == r[1]),
+         note="strided sample gathered on the host (256 KB cross the bus), order statistics selected on the device")
+    t0 = time.perf_counter(); g = ext.dem_minmax(d, False); tg = time.perf_counter() - t0
+    t0 = time.perf_counter(); r = o.min_max(d, False); tc = time.perf_counter() - t0
+    emit(config=f"min_max(clamp=false) {n} host array", gpu_ms=tg * 1e3, cpu_ms=tc * 1e3, equal=bool(np.float32(g[0]) == r[0] and np.float32(g[1]) == r[1]),
+         note="GPU time includes the 64 MiB H2D of a pageable host array, in 64 MiB chunks")
+    rr = vf.Renderer(64, 64)
+    rr.add_terrain(d, (1.0, 1.0), 1.0, "terrain")
+    t0 = time.perf_counter(); rr.add_terrain(d, (1.0, 1.0), 2.0, "terrain"); ta = time.perf_counter() - t0
+    t0 = time.perf_counter(); st = rr.terrain_stats(); ts = time.perf_counter() - t0
+    emit(config=f"Renderer.add_terrain {n} (one H2D, scale + percentile range on the device) / terrain_stats()", add_terrain_ms=ta * 1e3, terrain_stats_ms=ts * 1e3)
+    del rr
+# PNG delivery of the c3 frame
+sc = ext.Scene(1920, 1080, grid=4096, colormap="terrain")
+sc.set_height_from_r32f(dem4096); sc.set_shading("northstar", depth=False); sc.set_sun(35.0, 120.0); sc.set_exposure(1.1); sc.set_auto_height_range()
+for _ in range(4):
+    buf, sizes = sc.render_batch_png_raw(cams)
+t0 = time.perf_counter(); buf, sizes = sc.render_batch_png_raw(cams); tp = time.perf_counter() - t0
+import zlib
+emit(config="c3 frames as PNG files (render_batch_png_raw, 8 frames)", ms_per_frame=tp / len(cams) * 1e3, bytes_per_frame=int(sizes.mean()),
+     raw_bytes_per_frame=1920 * 1080 * 4, zlib_level6_bytes_for_comparison=None)
+del sc
 vf.grid_generate(1024, 1024)
 t0 = time.perf_counter(); a = vf.grid_generate(1024, 1024); tg = time.perf_counter() - t0
 t0 = time.perf_counter(); b = o.make_grid(1024, 1024, 1.0, 1.0); tc = time.perf_counter() - t0
@@ -106,3 +126,7 @@ if not quick:
     scene_case("c5 4K DEM16384 G=16384 depth magma exag 2", 3840, 2160, 16384, dem16k, "magma", "northstar", True, [default_cam] * 4,
                exag=2.0, cpu_frames=1)
     emit(config="c5 synthetic DEM generation", cpu_s=tgen)
+    ext.dem_minmax(dem16k, True)
+    t0 = time.perf_counter(); g = ext.dem_minmax(dem16k, True); tg = time.perf_counter() - t0
+    t0 = time.perf_counter(); r = o.min_max(dem16k, True); tc = time.perf_counter() - t0
+    emit(config="min_max(clamp=true) 16384^2 host array", gpu_ms=tg * 1e3, cpu_ms=tc * 1e3, equal=bool(np.float32(g[0]) == r[0] and np.float32(g[1]) == r[1]))

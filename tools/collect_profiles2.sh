@@ -39,7 +39,7 @@ LIB=vulkan-forge_b200/python/vulkan_forge/libvfcuda.so
   cuobjdump -sass $LIB 2>/dev/null | awk '
     /Function :/ { fn=$3 }
     /UTMALDG/ {c[fn,"UTMALDG"]++} /SYNCS/ {c[fn,"SYNCS"]++} /FFMA2/ {c[fn,"FFMA2"]++} /FMUL2/ {c[fn,"FMUL2"]++} /FADD2/ {c[fn,"FADD2"]++}
-    /PRMT/ {c[fn,"PRMT"]++} /STS.128/ {c[fn,"STS.128"]++} /RED\./ {c[fn,"RED"]++} /ATOMG/ {c[fn,"ATOMG"]++} /STL/ {c[fn,"STL"]++} /LDL/ {c[fn,"LDL"]++} /VOTE/ {c[fn,"VOTE"]++} /SHFL/ {c[fn,"SHFL"]++} /STG.E.128/ {c[fn,"STG.128"]++}
+    /PRMT/ {c[fn,"PRMT"]++} /STS.128/ {c[fn,"STS.128"]++} /RED[G.]/ {c[fn,"RED"]++} /ATOMG/ {c[fn,"ATOMG"]++} /STL/ {c[fn,"STL"]++} /LDL/ {c[fn,"LDL"]++} /VOTE/ {c[fn,"VOTE"]++} /SHFL/ {c[fn,"SHFL"]++} /STG.E.128/ {c[fn,"STG.128"]++}
     { if (fn != "") n[fn]++ }
     END { for (f in n) { printf "%s lines=%d", f, n[f]; split("UTMALDG SYNCS FFMA2 FMUL2 FADD2 PRMT STS.128 RED ATOMG VOTE SHFL STG.128 STL LDL", k, " "); for (i=1;i<=14;i++) if (c[f,k[i]]) printf " %s=%d", k[i], c[f,k[i]]; printf "\n" } }' | sort
   echo

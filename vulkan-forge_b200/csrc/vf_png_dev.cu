@@ -42,7 +42,7 @@ static uint32_t host_crc(const uint8_t* p, size_t n) {
 
 // filtered bytes a band aims for (a band is whole rows, at least one): VF_PNG_BAND_BYTES for tuning runs
 static size_t band_target() {
-    static const size_t v = [] { const char* e = getenv("VF_PNG_BAND_BYTES"); const long x = e ? atol(e) : 0; return (size_t)(x >= 1024 && x <= 32768 ? x : 32768); }();
+    static const size_t v = [] { const char* e = getenv("VF_PNG_BAND_BYTES"); const long x = e ? atol(e) : 0; return (size_t)(x >= 1024 && x <= 32768 ? x : 16384); }();
     return v;
 }
 size_t vf_png_dev_bound(int w, int h) {
@@ -73,7 +73,9 @@ int vf_png_dev_create(int w, int h, int slots, VfPngDev** out) {
         return vf_set_error(err == cudaErrorMemoryAllocation ? VF_E_OOM : VF_E_CUDA, "PNG encoder: %s: %s", what, cudaGetErrorString(err));
     };
     cudaError_t err;
-    if ((err = cudaFuncSetAttribute(k_png_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem_encode)) != cudaSuccess) return fail("shared memory", err);
+    e->small_bands = (((size_t)e->rows_per_band * stride + 3) / 4 + VF_PNG_THREADS - 1) / VF_PNG_THREADS <= 20;
+    if ((err = e->small_bands ? cudaFuncSetAttribute(k_png_encode<20, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem_encode)
+                              : cudaFuncSetAttribute(k_png_encode<40, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem_encode)) != cudaSuccess) return fail("shared memory", err);
     if ((err = cudaFuncSetAttribute(k_png_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)e->smem_pack)) != cudaSuccess) return fail("shared memory", err);
     if ((err = cudaMalloc(&e->d_bands, (size_t)e->nbands * e->band_cap)) != cudaSuccess) return fail("band buffer", err);
     if ((err = cudaMalloc(&e->d_band_size, (size_t)e->nbands * 4 * 4)) != cudaSuccess) return fail("band sizes", err);
@@ -121,8 +123,12 @@ int vf_png_dev_encode(VfPngDev* e, const uint8_t* d_frame, int slot, cudaStream_
     const uint8_t* pre = reinterpret_cast<const uint8_t*>(e->d_tables);
     const uint32_t* pb = e->d_tables + 16;
     const uint32_t* pp = pb + VF_PNG_PIECE;
-    k_png_encode<<<e->nbands, VF_PNG_THREADS, e->smem_encode, st>>>(d_frame, e->W, e->H, e->rows_per_band, e->raw_cap, e->band_cap,
-                                                                   e->d_bands, e->d_band_size, e->d_band_adler);
+    if (e->small_bands)
+        k_png_encode<20, 4><<<e->nbands, VF_PNG_THREADS, e->smem_encode, st>>>(d_frame, e->W, e->H, e->rows_per_band, e->raw_cap, e->band_cap,
+                                                                              e->d_bands, e->d_band_size, e->d_band_adler);
+    else
+        k_png_encode<40, 2><<<e->nbands, VF_PNG_THREADS, e->smem_encode, st>>>(d_frame, e->W, e->H, e->rows_per_band, e->raw_cap, e->band_cap,
+                                                                              e->d_bands, e->d_band_size, e->d_band_adler);
     k_png_pack<<<e->nbands, VF_PNG_THREADS, e->smem_pack, st>>>(e->d_bands, e->band_cap, e->d_band_size, e->d_band_adler, pre, pp, pb,
                                                                e->d_files + (size_t)slot * e->file_cap, e->file_cap, e->d_file_size + slot);
     VF_CUDA(cudaGetLastError());

@@ -8,6 +8,7 @@ struct VfPngDev {
     uint32_t W = 0, H = 0, rows_per_band = 0, nbands = 0;
     uint32_t raw_cap = 0, band_cap = 0, file_cap = 0;     // bytes: filtered band, encoded band, whole file (worst case)
     int slots = 0;
+    bool small_bands = false;                              // bands of <= 20 KiB: the <20, 4> instance of k_png_encode
     size_t smem_encode = 0, smem_pack = 0;
     uint8_t* d_bands = nullptr;                            // nbands x band_cap
     uint32_t* d_band_size = nullptr; uint32_t* d_band_adler = nullptr;

@@ -13,9 +13,12 @@
 // A band ends on a byte boundary (empty stored block, the Z_SYNC_FLUSH idiom), so bands concatenate as bytes.
 #pragma once
 
-#define VF_PNG_SEG_WORDS 40                     // >= ceil(ceil(65540 / 4) / 256): bands hold at most 64 KiB of filtered bytes
+// SEG_WORDS: most words of a band one thread analyses (a band holds at most 256 * SEG_WORDS words).  Two instances:
+// <20, 4> for bands up to 20 KiB (the default band is two rows of a 1080p frame: 64 registers, 50 KB of shared memory,
+// 4 CTAs per SM) and <40, 2> for frames whose single row is longer than that (up to 8192 pixels).
 // token table entry: bits 0..3 literal flags of the word's bytes | 4: a match starts here | 5..6: at which byte | 7..15: its length
-__global__ void __launch_bounds__(VF_PNG_THREADS)
+template <int SEG_WORDS, int MIN_CTAS>
+__global__ void __launch_bounds__(VF_PNG_THREADS, MIN_CTAS)
 k_png_encode(const uint8_t* __restrict__ frame, uint32_t W, uint32_t H, uint32_t rows_per_band, uint32_t raw_cap, uint32_t out_cap,
              uint8_t* __restrict__ bands, uint32_t* __restrict__ band_size, uint32_t* __restrict__ band_adler) {
     extern __shared__ __align__(16) unsigned char png_smem[];
@@ -37,19 +40,22 @@ k_png_encode(const uint8_t* __restrict__ frame, uint32_t W, uint32_t H, uint32_t
     __syncthreads();
     // ---- filter: type byte 1 (Sub) + pixel minus the pixel to its left, bytewise ----
     const uint32_t* px = reinterpret_cast<const uint32_t*>(frame) + (size_t)y0 * W;
-    for (uint32_t p = tid; p < rows * W; p += VF_PNG_THREADS) {
-        const uint32_t r = p / W, x = p - r * W;
-        const uint32_t cur = __ldg(px + p), prev = x ? __ldg(px + p - 1u) : 0u;
-        const uint32_t d = __vsub4(cur, prev);
-        uint8_t* o = raw + r * stride + 1u + 4u * x;
-        o[0] = (uint8_t)d; o[1] = (uint8_t)(d >> 8); o[2] = (uint8_t)(d >> 16); o[3] = (uint8_t)(d >> 24);
-        if (x == 0u) raw[r * stride] = 1u;
+    for (uint32_t r = 0; r < rows; ++r) {
+        const uint32_t* prow = px + (size_t)r * W;
+        uint8_t* orow = raw + r * stride + 1u;
+        for (uint32_t x = tid; x < W; x += VF_PNG_THREADS) {
+            const uint32_t cur = __ldg(prow + x), prev = x ? __ldg(prow + x - 1u) : 0u;
+            const uint32_t d = __vsub4(cur, prev);
+            uint8_t* o = orow + 4u * x;
+            o[0] = (uint8_t)d; o[1] = (uint8_t)(d >> 8); o[2] = (uint8_t)(d >> 16); o[3] = (uint8_t)(d >> 24);
+        }
+        if (tid == 0u) raw[r * stride] = 1u;
     }
     __syncthreads();
 
     // ---- analysis: thread t owns words [w0, w1), bytes [s0, s1) ----
-    constexpr int NW = (VF_PNG_SEG_WORDS + 7) / 8;              // 32-bit words of match bits per segment
-    const uint32_t segw = (Nw + VF_PNG_THREADS - 1u) / VF_PNG_THREADS;       // <= VF_PNG_SEG_WORDS
+    constexpr int NW = (SEG_WORDS + 7) / 8;              // 32-bit words of match bits per segment
+    const uint32_t segw = (Nw + VF_PNG_THREADS - 1u) / VF_PNG_THREADS;       // <= SEG_WORDS
     const uint32_t w0 = min(tid * segw, Nw), w1 = min(w0 + segw, Nw);
     const uint32_t s0 = min(4u * w0, N), s1 = min(4u * w1, N), nbytes_seg = s1 - s0;
     uint32_t m[NW + 1];                                          // match bit of byte s0 + k: bit k & 31 of m[k >> 5]
@@ -59,7 +65,7 @@ k_png_encode(const uint8_t* __restrict__ frame, uint32_t W, uint32_t H, uint32_t
     {
         uint32_t prev = w0 ? raww[w0 - 1u] : 0u;
 #pragma unroll
-        for (int k = 0; k < VF_PNG_SEG_WORDS; ++k) {
+        for (int k = 0; k < SEG_WORDS; ++k) {
             if (w0 + k < w1) {
                 const uint32_t cur = raww[w0 + k];
                 uint32_t bits = ((__vcmpeq4(cur, prev) & 0x01010101u) * 0x01020408u) >> 24;    // the four byte flags as bits 0..3

@@ -566,3 +566,29 @@ def test_device_png_slots_grow_when_a_file_does_not_fit(ext, vf):
         assert np.array_equal(_png_decode(b, W, H), want[k])
     buf, sizes = sc.render_batch_png_raw(cams)
     assert np.array_equal(_png_decode(bytes(buf[1, :sizes[1]]), W, H), want[1])
+
+
+def test_redo_of_a_batch_whose_image_is_no_longer_in_front(ext, oracle, luts, synthetic_dem):
+    """Found by the API fuzzer in round 2: a pipelined batch that has to be rendered again (its frames queued primitives
+    while the binning stage was left out) after a later upload has taken the front slot is redone from ITS image -- and
+    with that image's height bounds (the per-task corner test of k_geom_march).  Two images with different height ranges,
+    close-up cameras, several batches in flight, every batch compared with the oracle."""
+    W, H, G = 395, 89, 753
+    dems = [synthetic_dem(4, G) * np.float32(3.0), synthetic_dem(5, G)]
+    cams = [((0.12, 0.2, -0.05), (0.6, -0.1, 0.4), (0.0, 1.0, 0.0), 90.0, 0.01, 100.0),
+            ((4 * np.cos(1.0), 1.5, 4 * np.sin(1.0)), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 45.0, 0.1, 100.0)]
+    for depth in (False, True):
+        sc = ext.Scene(W, H, grid=G, colormap="viridis")
+        sc.set_shading("northstar", depth=depth)
+        sc.set_height_range(-0.4, 0.5)
+        blocks = sc.camera_blocks(cams)
+        want = [np.stack([oracle.render_terrain(W, H, G, d, blocks[i], luts["viridis"], mode=oracle.MODE_NORTHSTAR, depth=depth,
+                                                h_min=-0.4, h_max=0.5) for i in range(len(cams))]) for d in dems]
+        pend = []
+        for k in range(4):
+            sc.set_height_from_r32f_async(dems[k & 1])
+            pend.append((k & 1, sc.render_batch_rgba_async(cams)))
+        assert sc.render_metrics()["big_prims"] >= 0
+        for k, (which, tk) in enumerate(pend):
+            got = sc.collect(tk)
+            assert np.array_equal(got, want[which]), (depth, k, [int((got[i] != want[which][i]).any(-1).sum()) for i in range(len(cams))])

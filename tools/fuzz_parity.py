@@ -200,7 +200,8 @@ def fuzz_api(budget, seed):
             W, H = int(rng.integers(8, 500)), int(rng.integers(8, 400))
             G = int(rng.choice([rng.integers(16, 300), rng.integers(300, 1600)]))
             depth = bool(rng.integers(0, 2)); mode = str(rng.choice(["northstar", "shipped"]))
-            dems = [synthetic_dem(int(rng.integers(0, 7)), G) * np.float32(rng.choice([1.0, 3.0])) for _ in range(2)]
+            dem_par = [(int(rng.integers(0, 7)), float(rng.choice([1.0, 3.0]))) for _ in range(2)]
+            dems = [synthetic_dem(sd, G) * np.float32(sc_) for sd, sc_ in dem_par]
             cams = []
             for _ in range(int(rng.integers(1, 5))):
                 if rng.random() < 0.6:      # close-up: most triangles are big -> queues and pair buffers grow
@@ -209,7 +210,7 @@ def fuzz_api(budget, seed):
                 else:
                     a = float(rng.uniform(0, 6.28)); e = (4 * math.cos(a), float(rng.uniform(0.5, 3)), 4 * math.sin(a)); t = (0.0, 0.0, 0.0)
                 cams.append((e, t, (0.0, 1.0, 0.0), float(rng.choice([45.0, 90.0])), float(rng.choice([0.01, 0.1])), 100.0))
-            desc = dict(what="pipeline", W=W, H=H, G=G, depth=depth, mode=mode, cams=cams)
+            desc = dict(what="pipeline", W=W, H=H, G=G, depth=depth, mode=mode, dems=dem_par, cams=cams, failed=[])
             def scene():
                 sc = ext.Scene(W, H, grid=G, colormap="viridis")
                 sc.set_shading(mode, depth=depth); sc.set_height_range(-0.4, 0.5)
@@ -230,10 +231,23 @@ def fuzz_api(budget, seed):
                 pending.append((k & 1, sc.render_batch_rgba_async(cams)))
                 if len(pending) == 3:
                     which, tk = pending.pop(0)
-                    ok = ok and np.array_equal(sc.collect(tk), want[which])
-            for which, tk in pending:
-                ok = ok and np.array_equal(sc.collect(tk), want[which])
-            ok = ok and np.array_equal(sc.render_batch_rgba(cams), want[1])
+                    got = sc.collect(tk)
+                    if not np.array_equal(got, want[which]):
+                        ok = False; desc["failed"].append(("collect", k - 2, [int((got[i] != want[which][i]).any(-1).sum()) for i in range(len(cams))], dict(sc.render_metrics())["big_prims"]))
+            for j, (which, tk) in enumerate(pending):
+                got = sc.collect(tk)
+                if not np.array_equal(got, want[which]):
+                    ok = False; desc["failed"].append(("collect-tail", j, [int((got[i] != want[which][i]).any(-1).sum()) for i in range(len(cams))]))
+            got = sc.render_batch_rgba(cams)
+            if not np.array_equal(got, want[1]):
+                ok = False; desc["failed"].append(("sync-batch", [int((got[i] != want[1][i]).any(-1).sum()) for i in range(len(cams))]))
+            if not ok:                                      # is the reference scene itself stable?
+                ref_sc.set_height_from_r32f(dems[1])
+                again = []
+                for c in cams:
+                    ref_sc.set_camera_look_at(*c)
+                    again.append(ref_sc.render_rgba().copy())
+                desc["ref_unstable"] = [int((again[i] != want[1][i]).any(-1).sum()) for i in range(len(cams))]
             del sc, ref_sc
         n += 1
         if not ok:

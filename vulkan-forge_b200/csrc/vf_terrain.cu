@@ -888,7 +888,7 @@ static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
 
 // ---- pipelined interface: uploads and batches overlap across calls -------------------------------
 static void scene_swap_images(vf_scene* s) {
-    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back); std::swap(s->d_hmm, s->d_hmm_back); std::swap(s->d_hmm, s->d_hmm_back);
+    std::swap(s->d_dem, s->d_dem_back); std::swap(s->d_hgrid, s->d_hgrid_back); std::swap(s->d_hmm, s->d_hmm_back);
     std::swap(s->dem_map, s->dem_map_b); std::swap(s->dem_map_gm[0], s->dem_map_gm_b[0]); std::swap(s->dem_map_gm[1], s->dem_map_gm_b[1]);
 }
 
@@ -973,6 +973,8 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
     VF_CUDA(cudaEventRecord(s->ev_up1, s->upload_stream));
     s->upload_timed = true;
     VF_CUDA(cudaEventRecord(s->ev_uploaded, s->upload_stream));
+    static const bool dbg_sync = getenv("VF_DEBUG_SYNC_UPLOAD") != nullptr;      // debugging aid: no overlap of upload and frames
+    if (dbg_sync) VF_CUDA(cudaStreamSynchronize(s->upload_stream));
     s->back_pending = true;
     return VF_OK;
 }

@@ -201,7 +201,8 @@ def fuzz_api(budget, seed):
             G = int(rng.choice([rng.integers(16, 300), rng.integers(300, 1600)]))
             depth = bool(rng.integers(0, 2)); mode = str(rng.choice(["northstar", "shipped"]))
             dem_par = [(int(rng.integers(0, 7)), float(rng.choice([1.0, 3.0]))) for _ in range(2)]
-            dems = [synthetic_dem(sd, G) * np.float32(sc_) for sd, sc_ in dem_par]
+            Gd = G if rng.random() < 0.7 else int(rng.integers(8, 500))     # DEM size != grid: the vertex-height image is resampled per upload
+            dems = [synthetic_dem(sd, Gd) * np.float32(sc_) for sd, sc_ in dem_par]
             cams = []
             for _ in range(int(rng.integers(1, 5))):
                 if rng.random() < 0.6:      # close-up: most triangles are big -> queues and pair buffers grow
@@ -210,7 +211,7 @@ def fuzz_api(budget, seed):
                 else:
                     a = float(rng.uniform(0, 6.28)); e = (4 * math.cos(a), float(rng.uniform(0.5, 3)), 4 * math.sin(a)); t = (0.0, 0.0, 0.0)
                 cams.append((e, t, (0.0, 1.0, 0.0), float(rng.choice([45.0, 90.0])), float(rng.choice([0.01, 0.1])), 100.0))
-            desc = dict(what="pipeline", W=W, H=H, G=G, depth=depth, mode=mode, dems=dem_par, cams=cams, failed=[])
+            desc = dict(what="pipeline", W=W, H=H, G=G, Gd=Gd, depth=depth, mode=mode, dems=dem_par, cams=cams, failed=[])
             def scene():
                 sc = ext.Scene(W, H, grid=G, colormap="viridis")
                 sc.set_shading(mode, depth=depth); sc.set_height_range(-0.4, 0.5)

@@ -121,6 +121,12 @@ int vf_dem_ingest_f32(const float *src, size_t n, float scale, float *dst);
  * with VF_E_INVALID.  All calls share that array: calls that overlap on the GPU race -- serialise them (one stream). */
 int vf_dem_minmax_noalloc_async(const float *d_data, size_t n, int clamp, float *d_out2, void *cuda_stream);
 
+/* Arithmetic self-test (no counterpart in the reference: a diagnostic of this library).  The kernels replace most
+ * IEEE divisions of the shading by the shorter instruction sequence the division itself takes for operands of ordinary
+ * magnitude (csrc/vf_device.cuh); this runs n_groups groups of random and special operands through those helpers and
+ * the plain division on the device and counts the results that differ in any bit.  *mismatches must come back 0. */
+int vf_selftest_div(uint64_t n_groups, uint32_t seed, uint64_t *mismatches);
+
 /* ---- device-resident height images ----------------------------------------------------------
  * replaces: the Vec<f32> that Renderer.add_terrain keeps on the host (src/lib.rs:351-418) and everything computed
  * from it (terrain_stats :424-429, normalize_terrain :478-493, upload_height_r32f :496-571).  The array crosses

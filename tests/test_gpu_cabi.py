@@ -139,3 +139,17 @@ def test_cabi_march_equals_tiled_geometry(lib, synthetic_dem, monkeypatch):
                 b = _scene_frame(lib, W, H, G, dem, u, mode, depth, -0.3, 0.4)
                 monkeypatch.delenv("VF_GEOM_TILED", raising=False)
                 assert np.array_equal(a, b), (W, H, G, mode, depth)
+
+
+def test_cabi_division_helpers_equal_ieee_division(lib):
+    """vf_selftest_div: the shading's division helpers (csrc/vf_device.cuh: the instruction sequence div.rn / rcp.rn
+    take themselves for operands of ordinary magnitude, without the range check and with a shared reciprocal) against
+    the plain correctly rounded division, on the device, bit for bit: 2^27 groups of random, special, window-edge and
+    zero operands per seed (13 comparisons per group)."""
+    lib.vf_selftest_div.argtypes = [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]
+    for seed in (1, 20261105):
+        bad = C.c_uint64(123)
+        assert lib.vf_selftest_div(1 << 27, seed, C.byref(bad)) == 0, lib.vf_last_error()
+        assert bad.value == 0
+    assert lib.vf_selftest_div(0, 0, C.byref(bad)) == 0 and bad.value == 0
+    assert lib.vf_selftest_div(16, 0, None) != 0

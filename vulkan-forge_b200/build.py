@@ -21,7 +21,7 @@ NVCC = os.environ.get("VF_NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("VF_CXX", "/usr/bin/g++")
 
 CUDA_SRCS = ["vf_context.cu", "vf_terrain.cu", "vf_dem.cu", "vf_misc.cu", "vf_png_dev.cu", "vf_png.cpp"]
-CUDA_DEPS = CUDA_SRCS + ["vf_device.cuh", "vf_terrain_kernels.cuh", "vf_geom_march.cuh", "vf_internal.h", "vf_png_dev.h", "vf_png_kernels.cuh", "vf_png_encode.cuh", "vf_png_encode_tail.inc", "vf_png_encode_emit.inc", "vf_png_pack.cuh", "vf_lut_data.inc",
+CUDA_DEPS = CUDA_SRCS + ["vf_device.cuh", "vf_terrain_kernels.cuh", "vf_geom_march.cuh", "vf_raster_lean.cuh", "vf_internal.h", "vf_png_dev.h", "vf_png_kernels.cuh", "vf_png_encode.cuh", "vf_png_encode_tail.inc", "vf_png_encode_emit.inc", "vf_png_pack.cuh", "vf_lut_data.inc",
                          "../../include/vf_cuda.h"]
 HOST_DEPS = ["host/module.cpp", "host/module_renderer.inc", "host/vf_camera.hpp", "../../include/vf_cuda.h"]
 

@@ -127,7 +127,7 @@ static __device__ __noinline__ int vf_gm_rebuild(const VfFrame& f, const VfAxis*
 // (they fit 32 bits: 0 <= E_i < 2^31 on a covered sample of a micro or serial triangle).  vf_barycentric divides
 // by e0 + e1 + e2, which is twice the triangle's area at every sample: rinv = 1 / float(-area2) is taken once per
 // triangle (vf_gm_rinv) and the weights are the same floats as vf_barycentric's.
-__device__ __forceinline__ float vf_gm_rinv(int64_t area2) { return __fdiv_rn(1.0f, (float)(-area2)); }
+__device__ __forceinline__ float vf_gm_rinv(int64_t area2) { return vf_rcp1((float)(-area2)); }
 __device__ __forceinline__ void vf_gm_emit_depth(unsigned long long* __restrict__ key64, const VfSubTri& t, float rinv, uint32_t nbias,
                                                  uint32_t prim, uint32_t e0, uint32_t e1, uint32_t e2) {
     float b[3];

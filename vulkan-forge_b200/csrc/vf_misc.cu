@@ -179,3 +179,86 @@ extern "C" void vf_height_destroy(vf_height* t) {
     cudaFree(t->d);
     delete t;
 }
+
+// ---------------------------------------------------------------------------------------
+// vf_selftest_div: the division helpers of vf_device.cuh (vf_rcp1 / vf_rcp3 / vf_div1 / vf_div_by / vf_div3) against the
+// correctly rounded intrinsic they stand for, bit for bit, on the device.  Operands: a counter-based generator mixes
+// plain random bit patterns (every exponent, subnormals, infinities, NaNs), values of the magnitudes the shading sees,
+// values around the helpers' window limits, and exact zeros.  No reference counterpart: a diagnostic of this library.
+__device__ __forceinline__ uint32_t vf_st_hash(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ float vf_st_operand(uint32_t h) {
+    const uint32_t kind = h & 7u, bits = vf_st_hash(h ^ 0x9e3779b9u);
+    if (kind < 2u) return __uint_as_float(bits);                                             // anything at all
+    if (kind == 2u) {                                                                         // around the window limits
+        const uint32_t e = (bits & 1u) ? 127u - 31u : 127u + 31u;
+        return __uint_as_float((bits & 0x80000000u) | ((e - 1u + ((bits >> 1) % 3u)) << 23) | ((bits >> 3) & ((bits & 4u) ? 0x7fffffu : 0x3u)));
+    }
+    if (kind == 3u && (bits & 0xf0u) == 0u) return __uint_as_float(bits & 0x80000000u);       // a zero now and then
+    const uint32_t e = 127u - 20u + (bits >> 8) % 40u;                                        // 2^-20 .. 2^20: the shading's range
+    return __uint_as_float((bits & 0x80000000u) | (e << 23) | (vf_st_hash(bits) & 0x7fffffu));
+}
+__device__ __forceinline__ bool vf_st_same(float x, float y) {
+    return __float_as_uint(x) == __float_as_uint(y) || (x != x && y != y);
+}
+__global__ void __launch_bounds__(256)
+k_selftest_div(unsigned long long n, uint32_t seed, unsigned long long* __restrict__ bad) {
+    unsigned long long mine = 0ull;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint32_t h = vf_st_hash((uint32_t)i * 0x9e3779b1u + (uint32_t)(i >> 32) + seed);
+        float a[5], b[3], q[5], want;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) a[k] = vf_st_operand(vf_st_hash(h + 0x1000193u * (uint32_t)(k + 1)));
+#pragma unroll
+        for (int k = 0; k < 3; ++k) b[k] = vf_st_operand(vf_st_hash(h ^ (0x85ebca6bu * (uint32_t)(k + 7))));
+        if (h & 0x100u) {                                        // groups that stay inside the window more often
+#pragma unroll
+            for (int k = 0; k < 5; ++k) a[k] = vf_st_operand((vf_st_hash(h + 31u * (uint32_t)k) & ~7u) | 4u);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) b[k] = vf_st_operand((vf_st_hash(h + 77u * (uint32_t)k) & ~7u) | 5u);
+        }
+        uint32_t miss = 0u;
+        miss += vf_st_same(vf_rcp1(b[0]), __fdiv_rn(1.0f, b[0])) ? 0u : 1u;
+        miss += vf_st_same(vf_rcp1(b[0]), __frcp_rn(b[0])) ? 0u : 1u;
+        float r3[3];
+        vf_rcp3(b, r3);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) miss += vf_st_same(r3[k], __fdiv_rn(1.0f, b[k])) ? 0u : 1u;
+        miss += vf_st_same(vf_div1(a[0], b[1]), __fdiv_rn(a[0], b[1])) ? 0u : 1u;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) q[k] = -1.0f;
+        vf_div_by<5>(a, b[2], q, 0x1du);                         // numerators 0, 2, 3, 4
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            want = ((0x1du >> k) & 1u) ? __fdiv_rn(a[k], b[2]) : -1.0f;
+            miss += vf_st_same(q[k], want) ? 0u : 1u;
+        }
+        vf_div3(a, b, q);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) miss += vf_st_same(q[k], __fdiv_rn(a[k], b[k])) ? 0u : 1u;
+        mine += miss;
+    }
+    if (mine) atomicAdd(bad, mine);
+}
+
+extern "C" int vf_selftest_div(uint64_t n_groups, uint32_t seed, uint64_t* mismatches) {
+    if (!mismatches) return vf_set_error(VF_E_INVALID, "null output");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    unsigned long long* d = (unsigned long long*)vf_scratch(sizeof(unsigned long long));
+    if (!st || !d) return VF_E_CUDA;
+    VF_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long), st));
+    if (n_groups) {
+        k_selftest_div<<<148 * 8, 256, 0, st>>>((unsigned long long)n_groups, seed, d);
+        VF_CUDA(cudaGetLastError());
+    }
+    unsigned long long hres = 0ull;
+    VF_CUDA(cudaMemcpyAsync(&hres, d, sizeof(hres), cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
+    *mismatches = (uint64_t)hres;
+    return VF_OK;
+}

@@ -11,6 +11,7 @@
 
 #include "vf_internal.h"
 #include "vf_geom_march.cuh"
+#include "vf_raster_lean.cuh"
 #include "vf_png_dev.h"
 
 // cuTensorMapEncodeTiled through the runtime's driver entry point (libcuda is not linked)
@@ -56,6 +57,7 @@ struct vf_scene {
     uint2* d_segtab = nullptr;           // k_geom_march row segments (first row, rows), rebuilt when G changes
     uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0, segtab_nfull = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
+    uint2* d_shade_list = nullptr;           // W*H entries: covered pixels of the frame (vf_raster_lean.cuh)
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
@@ -146,6 +148,7 @@ static uint64_t scene_vram_bytes(const vf_scene* s) {
     b += (uint64_t)s->G * sizeof(VfAxis) + 256 * sizeof(float4);
     b += (uint64_t)s->n_slots * s->W * s->H * 4;                       // frame slots
     b += (uint64_t)s->W * s->H * 8;                                    // visibility buffer
+    b += s->d_shade_list ? (uint64_t)s->W * s->H * 8 : 0;              // covered-pixel list
     b += s->d_vis ? (uint64_t)s->W * s->H * 4 : 0;
     b += ((uint64_t)s->n_tiles + VF_CNT_WORDS) * 4 + ((uint64_t)s->n_tiles + 5) * 4 + (uint64_t)s->n_tiles * 4;
     b += 3ull * s->capacity * 4 + (uint64_t)s->big_capacity * 4 + (uint64_t)s->segtab_cap * 8;
@@ -158,7 +161,7 @@ static void scene_free(vf_scene* s) {
     cudaFree(s->d_dem); cudaFree(s->d_axis); cudaFree(s->d_lut); cudaFree(s->d_frame);
     cudaFree(s->d_vis); cudaFree(s->d_tile_count); cudaFree(s->d_tile_off);
     cudaFree(s->d_tile_cursor); cudaFree(s->d_pair_tile); cudaFree(s->d_pair_prim);
-    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_big); cudaFree(s->d_flag); cudaFree(s->d_segtab);
+    cudaFree(s->d_sorted); cudaFree(s->d_visbuf); cudaFree(s->d_shade_list); cudaFree(s->d_big); cudaFree(s->d_flag); cudaFree(s->d_segtab);
     cudaFree(s->d_dem_back); cudaFree(s->d_hgrid); cudaFree(s->d_hgrid_back); cudaFree(s->d_hmm); cudaFree(s->d_hmm_back);
     if (s->upload_stream) cudaStreamDestroy(s->upload_stream);
     if (s->ev_uploaded) cudaEventDestroy(s->ev_uploaded);
@@ -450,6 +453,11 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
         (void)cudaGetLastError();
         return vf_set_error(VF_E_OOM, "visibility buffer allocation failed");
     }
+    if ((w & 3) == 0 && cudaMalloc(&s->d_shade_list, (size_t)w * h * sizeof(uint2)) != cudaSuccess) {
+        scene_free(s);
+        (void)cudaGetLastError();
+        return vf_set_error(VF_E_OOM, "covered-pixel list allocation failed");
+    }
     const float zero = 0.0f;                                   // 1x1 zero image until set_height
     rc = scene_upload_dem(s, &zero, 1, 1);
     if (rc) { scene_free(s); return rc; }
@@ -669,7 +677,8 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
     static const bool bin_always = getenv("VF_BIN_ALWAYS") != nullptr;
-    if (s->bin_hold == 0 && !bin_always) {
+    const bool skip_bins = s->bin_hold == 0 && !bin_always;
+    if (skip_bins) {
         s->submit_skipped_bins = true;
     } else {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
         if (s->bin_hold) --s->bin_hold;
@@ -693,8 +702,24 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     const uint32_t hgp = s->d_hgrid ? s->hpitch : s->pitch;
 #define VF_RASTER_LAUNCH(M, D) k_raster<M, D><<<dim3(s->tiles_x, s->tiles_y), 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, \
         s->d_visbuf, s->d_tile_off, s->d_sorted, s->d_counters, clear, frame, d_vis, s->d_maxpairs)
-    if (f.mode == VF_MODE_SHIPPED) { if (f.depth) VF_RASTER_LAUNCH(0, true); else VF_RASTER_LAUNCH(0, false); }
-    else                           { if (f.depth) VF_RASTER_LAUNCH(1, true); else VF_RASTER_LAUNCH(1, false); }
+    // Frames that skip the binning stage take the two kernels without the merge / clipper paths (vf_raster_lean.cuh): a
+    // streaming resolve that lists the covered pixels, then a dense shading pass over the list.  If the frame did queue
+    // something, k_resolve_lean reports it like k_raster and the frame is rendered again.
+    static const bool raster_full = getenv("VF_RASTER_FULL") != nullptr;
+    if (skip_bins && !raster_full && s->d_shade_list != nullptr) {
+        int& sms = g_dev_cache[s->device & 63].sm_count;
+        if (!sms) VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
+        const uint32_t w4 = s->W >> 2, quads = w4 * s->H, half = ((quads + 1u) / 2u + 255u) & ~255u;
+        const uint32_t w4_inv = (uint32_t)(0x100000000ull / w4 > 0xffffffffull ? 0xffffffffull : 0x100000000ull / w4);
+        if (f.depth) k_resolve_lean<true><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
+        else         k_resolve_lean<false><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
+        const int ctas = sms * VF_SHADE_CTAS;
+        if (f.mode == VF_MODE_SHIPPED) k_shade_list<0><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->d_shade_list, clear, frame);
+        else                           k_shade_list<1><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->d_shade_list, clear, frame);
+    } else {
+        if (f.mode == VF_MODE_SHIPPED) { if (f.depth) VF_RASTER_LAUNCH(0, true); else VF_RASTER_LAUNCH(0, false); }
+        else                           { if (f.depth) VF_RASTER_LAUNCH(1, true); else VF_RASTER_LAUNCH(1, false); }
+    }
 #undef VF_RASTER_LAUNCH
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());

@@ -56,7 +56,7 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_SERIAL_AREA 4096    // shorter bbox axis and at most this many pixels of area; larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
-enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_WORDS = 8 };
+enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_SHADE = 5, VF_CNT_WORDS = 8 };
 
 // ---------------------------------------------------------------------------------------
 __global__ void k_axis(VfAxis* __restrict__ axis, uint32_t G, float step, float gm1,
@@ -637,15 +637,18 @@ __device__ __forceinline__ uint32_t vf_shade_at(const VfFrame& f, const VfSubTri
     float b[3], a[5];
     vf_barycentric(e, b);
     const float iw = fmaf(b[2], t.v[2].invw, fmaf(b[1], t.v[1].invw, __fmul_rn(b[0], t.v[0].invw)));
+    // NORTHSTAR reads u, v, h; SHIPPED reads h, x, z (vf_fragment_stage): the others are never computed
+    constexpr uint32_t used = MODE == 1 ? 0x07u : MODE == 0 ? 0x1cu : 0x1fu;
+    float num[5];
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
-        // NORTHSTAR reads u, v, h; SHIPPED reads h, x, z (vf_fragment_stage): the others are never computed
-        if ((MODE == 1 && k >= 3) || (MODE == 0 && k < 2)) { a[k] = 0.0f; continue; }
-        const float num = fmaf(b[2], __fmul_rn(t.v[2].a[k], t.v[2].invw),
-                          fmaf(b[1], __fmul_rn(t.v[1].a[k], t.v[1].invw),
-                               __fmul_rn(b[0], __fmul_rn(t.v[0].a[k], t.v[0].invw))));
-        a[k] = __fdiv_rn(num, iw);
+        a[k] = 0.0f; num[k] = 0.0f;
+        if (!((used >> k) & 1u)) continue;
+        num[k] = fmaf(b[2], __fmul_rn(t.v[2].a[k], t.v[2].invw),
+                 fmaf(b[1], __fmul_rn(t.v[1].a[k], t.v[1].invw),
+                      __fmul_rn(b[0], __fmul_rn(t.v[0].a[k], t.v[0].invw))));
     }
+    vf_div_by<5>(num, iw, a, used);                      // a[k] = num[k] / iw
     return vf_fragment_stage<MODE, true>(f, a, dem, lut, thr);
 }
 
@@ -666,6 +669,73 @@ vf_shade_clipped(const VfFrame& f, const VfAxis* __restrict__ axis, const float*
         done = true;
     });
     return rgba;
+}
+
+// Shading of a pixel from its winning primitive, in three steps so that k_raster_lean can fetch the heights ahead of time.
+// cell of a primitive -> (column i, row j) without a division
+__device__ __forceinline__ void vf_winner_cell(const VfFrame& f, uint32_t prim, uint32_t& i, uint32_t& j) {
+    const uint32_t cell = prim >> 1, gm = f.G - 1u;
+    j = __umulhi(cell, f.gm_inv); i = cell - j * gm;            // j <= cell / gm <= j + 2
+    if (i >= gm) { i -= gm; ++j; }
+    if (i >= gm) { i -= gm; ++j; }
+}
+// T0 = (a, c, b), T1 = (b, c, d) (src/terrain/mod.rs:575-583): vertex 0 = (i + k, j), 1 = (i, j + 1), 2 = (i + 1, j + k).
+// Offsets of the three vertex heights in the G x G vertex-height image (pitch in floats).
+__device__ __forceinline__ void vf_winner_height_offsets(uint32_t i, uint32_t j, uint32_t k, uint32_t hpitch, size_t off[3]) {
+    const size_t o = (size_t)j * hpitch + i;
+    off[0] = o + k; off[1] = o + hpitch; off[2] = o + (k ? hpitch + 1u : 1u);
+}
+// the same heights gathered from the DEM through the axis table (no vertex-height image)
+__device__ __forceinline__ void vf_winner_heights_dem(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
+                                                      uint32_t i, uint32_t j, uint32_t k, float h[3]) {
+    const int tx0 = axis[i].tx, tx1 = axis[i + 1u].tx, ty0 = axis[j].ty, ty1 = axis[j + 1u].ty;
+    h[0] = __ldg(dem + (size_t)ty0 * f.dem_pitch + (k ? tx1 : tx0));
+    h[1] = __ldg(dem + (size_t)ty1 * f.dem_pitch + tx0);
+    h[2] = __ldg(dem + (size_t)(k ? ty1 : ty0) * f.dem_pitch + tx1);
+}
+// The winner's three vertices from their heights and the axis table (no clip machinery, no stack), then the pixel's colour.
+// false (rgba untouched): a vertex lies outside near / far / the guard band, the triangle needs the clipper.
+template <int MODE>
+__device__ __forceinline__ bool
+vf_shade_winner_h(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem, const float4* __restrict__ lut,
+                  const float* __restrict__ thr, uint32_t i, uint32_t j, uint32_t k, const float h[3], int px, int py, uint32_t& rgba) {
+    const float2 ax0 = __ldg(reinterpret_cast<const float2*>(axis + i)), ax1 = __ldg(reinterpret_cast<const float2*>(axis + i + 1u));
+    const float2 az0 = __ldg(reinterpret_cast<const float2*>(axis + j)), az1 = __ldg(reinterpret_cast<const float2*>(axis + j + 1u));
+    VfVtx tri[3];
+    const float2 axk = k ? ax1 : ax0, azk = k ? az1 : az0;
+    vf_vertex_stage<MODE>(f, axk.x, az0.x, axk.y, az0.y, h[0], tri[0]);
+    vf_vertex_stage<MODE>(f, ax0.x, az1.x, ax0.y, az1.y, h[1], tri[1]);
+    vf_vertex_stage<MODE>(f, ax1.x, azk.x, ax1.y, azk.y, h[2], tri[2]);
+    const uint32_t f0 = vf_clip_flags(tri[0].c), f1 = vf_clip_flags(tri[1].c), f2 = vf_clip_flags(tri[2].c);
+    if (!(f0 & f1 & f2 & 64u)) return false;             // not every vertex inside near / far / the guard band
+    VfSubTri t;
+    const float w3[3] = {tri[0].c[3], tri[1].c[3], tri[2].c[3]};
+    float iw3[3];
+    vf_rcp3(w3, iw3);
+#pragma unroll
+    for (int v = 0; v < 3; ++v) vf_to_screen_w(f, tri[v], iw3[v], t.v[v]);
+    const int32_t sx = px * VF_SUBPIX + VF_HALFPIX, sy = py * VF_SUBPIX + VF_HALFPIX;
+    const int64_t e[3] = {vf_edge(t.v[1], t.v[2], sx, sy), vf_edge(t.v[2], t.v[0], sx, sy), vf_edge(t.v[0], t.v[1], sx, sy)};
+    rgba = vf_shade_at<MODE>(f, t, e, dem, lut, thr);
+    return true;
+}
+template <int MODE>
+__device__ __forceinline__ bool
+vf_shade_winner(const VfFrame& f, const VfAxis* __restrict__ axis, const float* __restrict__ dem, const float* __restrict__ hgrid,
+                uint32_t hpitch, const float4* __restrict__ lut, const float* __restrict__ thr, uint32_t prim, int px, int py,
+                uint32_t& rgba) {
+    uint32_t i, j;
+    const uint32_t k = prim & 1u;
+    vf_winner_cell(f, prim, i, j);
+    float h[3];
+    if (hgrid != nullptr) {
+        size_t off[3];
+        vf_winner_height_offsets(i, j, k, hpitch, off);
+        h[0] = __ldg(hgrid + off[0]); h[1] = __ldg(hgrid + off[1]); h[2] = __ldg(hgrid + off[2]);
+    } else {
+        vf_winner_heights_dem(f, axis, dem, i, j, k, h);
+    }
+    return vf_shade_winner_h<MODE>(f, axis, dem, lut, thr, i, j, k, h, px, py, rgba);
 }
 
 // hgrid: the G x G image of vertex heights (vf_terrain.cu: the resampled image, or the DEM itself when the grid maps
@@ -736,39 +806,9 @@ k_raster(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     else id1 = (uint32_t)key;
     uint32_t rgba = clear_rgba;
     if (id1 != 0u && inb) {
-        const uint32_t prim = id1 - 1u, cell = prim >> 1, k = prim & 1u, gm = f.G - 1u;
-        uint32_t j = __umulhi(cell, f.gm_inv), i = cell - j * gm;       // j <= cell / gm <= j + 2
-        if (i >= gm) { i -= gm; ++j; }
-        if (i >= gm) { i -= gm; ++j; }
-        // T0 = (a, c, b), T1 = (b, c, d) (src/terrain/mod.rs:575-583): vertex 0 = (i + k, j), 1 = (i, j + 1), 2 = (i + 1, j + k)
-        const float2 ax0 = __ldg(reinterpret_cast<const float2*>(axis + i)), ax1 = __ldg(reinterpret_cast<const float2*>(axis + i + 1u));
-        const float2 az0 = __ldg(reinterpret_cast<const float2*>(axis + j)), az1 = __ldg(reinterpret_cast<const float2*>(axis + j + 1u));
-        float h0, h1, h2;
-        if (hgrid != nullptr) {
-            const float* row0 = hgrid + (size_t)j * hpitch + i;
-            h0 = __ldg(row0 + k); h1 = __ldg(row0 + hpitch); h2 = __ldg(row0 + (k ? hpitch + 1u : 1u));
-        } else {
-            const int tx0 = axis[i].tx, tx1 = axis[i + 1u].tx, ty0 = axis[j].ty, ty1 = axis[j + 1u].ty;
-            h0 = __ldg(dem + (size_t)ty0 * f.dem_pitch + (k ? tx1 : tx0));
-            h1 = __ldg(dem + (size_t)ty1 * f.dem_pitch + tx0);
-            h2 = __ldg(dem + (size_t)(k ? ty1 : ty0) * f.dem_pitch + tx1);
-        }
-        VfVtx tri[3];
-        const float2 axk = k ? ax1 : ax0, azk = k ? az1 : az0;
-        vf_vertex_stage<MODE>(f, axk.x, az0.x, axk.y, az0.y, h0, tri[0]);
-        vf_vertex_stage<MODE>(f, ax0.x, az1.x, ax0.y, az1.y, h1, tri[1]);
-        vf_vertex_stage<MODE>(f, ax1.x, azk.x, ax1.y, azk.y, h2, tri[2]);
-        const uint32_t f0 = vf_clip_flags(tri[0].c), f1 = vf_clip_flags(tri[1].c), f2 = vf_clip_flags(tri[2].c);
-        if (f0 & f1 & f2 & 64u) {                           // every vertex inside near / far / the guard band
-            VfSubTri t;
-#pragma unroll
-            for (int v = 0; v < 3; ++v) vf_to_screen(f, tri[v], t.v[v]);
-            const int32_t sx = px * VF_SUBPIX + VF_HALFPIX, sy = py * VF_SUBPIX + VF_HALFPIX;
-            const int64_t e[3] = {vf_edge(t.v[1], t.v[2], sx, sy), vf_edge(t.v[2], t.v[0], sx, sy), vf_edge(t.v[0], t.v[1], sx, sy)};
-            rgba = vf_shade_at<MODE>(f, t, e, dem, lut, s_thr);
-        } else {
+        const uint32_t prim = id1 - 1u;
+        if (!vf_shade_winner<MODE>(f, axis, dem, hgrid, hpitch, lut, s_thr, prim, px, py, rgba))
             rgba = vf_shade_clipped<MODE>(f, axis, dem, lut, s_thr, prim, px, py, clear_rgba);
-        }
     }
     if (out_vis && inb) out_vis[(size_t)py * f.W + px] = id1;
 

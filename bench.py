@@ -352,9 +352,9 @@ def main():
             "e2e_png": {"value": png_fps, "unit": "frames/s", "steps": png_steps, "h2d_bytes_per_step": int(dem.nbytes + F * 176),
                         "d2h_bytes_per_step": int(png_bytes // png_steps),
                         "note": "same steps, frames delivered as .png files in pinned host memory, encoded on the device (Scene.render_batch_png_raw)"},
-            "gpu_launches": args.steps * F * 2,   # k_geom_march + k_raster per frame (value leg); k_binsort is not launched while frames queue nothing for it
+            "gpu_launches": args.steps * F * 3,   # k_geom_march + k_resolve_lean + k_shade_list per frame (value leg); k_binsort / k_raster only for frames that queue large or clipped triangles
             "parity": parity,
-            "roofline": {"bound": "hbm", "limited_by": "instruction issue (see issue)", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_raster"}[dom],
+            "roofline": {"bound": "hbm", "limited_by": "instruction issue (see issue)", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_resolve_lean + k_shade_list"}[dom],
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": ncu_traffic({"ms_geom": "k_geom", "ms_bin": "k_bin", "ms_raster": "k_raster"}[dom]),
                          "traffic_source": "committed ncu --set full capture (profiles/dram_traffic.json), not measured in this run",

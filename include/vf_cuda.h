@@ -126,6 +126,9 @@ int vf_dem_minmax_noalloc_async(const float *d_data, size_t n, int clamp, float 
  * magnitude (csrc/vf_device.cuh); this runs n_groups groups of random and special operands through those helpers and
  * the plain division on the device and counts the results that differ in any bit.  *mismatches must come back 0. */
 int vf_selftest_div(uint64_t n_groups, uint32_t seed, uint64_t *mismatches);
+/* The same for the sRGB8 store: the shading's encoder (approximate OETF, then one correction against the exact
+ * thresholds) against the binary search over those thresholds, for EVERY float in [0, 1] and 2^24 values outside. */
+int vf_selftest_srgb(uint64_t *mismatches);
 
 /* ---- device-resident height images ----------------------------------------------------------
  * replaces: the Vec<f32> that Renderer.add_terrain keeps on the host (src/lib.rs:351-418) and everything computed

@@ -153,3 +153,13 @@ def test_cabi_division_helpers_equal_ieee_division(lib):
         assert bad.value == 0
     assert lib.vf_selftest_div(0, 0, C.byref(bad)) == 0 and bad.value == 0
     assert lib.vf_selftest_div(16, 0, None) != 0
+
+
+def test_cabi_srgb_encoder_equals_threshold_search_for_every_float(lib):
+    """vf_selftest_srgb: the shading's sRGB8 encoder (approximate OETF + one correction step) against the binary search
+    over the exact thresholds (whose codes tests/test_pixel_known_answers.py checks against the float64 OETF), for all 1 065 353 217
+    floats of [0, 1] and 2^24 bit patterns outside (above 1, negative, infinities, NaNs)."""
+    lib.vf_selftest_srgb.argtypes = [C.POINTER(C.c_uint64)]
+    bad = C.c_uint64(7)
+    assert lib.vf_selftest_srgb(C.byref(bad)) == 0, lib.vf_last_error()
+    assert bad.value == 0

@@ -592,3 +592,30 @@ def test_redo_of_a_batch_whose_image_is_no_longer_in_front(ext, oracle, luts, sy
         for k, (which, tk) in enumerate(pend):
             got = sc.collect(tk)
             assert np.array_equal(got, want[which]), (depth, k, [int((got[i] != want[which][i]).any(-1).sum()) for i in range(len(cams))])
+
+
+@pytest.mark.parametrize("size", [(640, 360), (322, 181)])
+def test_list_shading_equals_tile_kernel(ext, vf, synthetic_dem, monkeypatch, size):
+    """Frames that queue nothing for the binning stage are shaded by k_resolve_lean + k_shade_list (covered-pixel list,
+    csrc/vf_raster_lean.cuh); VF_RASTER_FULL at scene creation keeps the tile kernel k_raster in every frame, and so does a
+    width that is not a multiple of 4.  Same bytes either way, in both shading modes, with and without the depth test."""
+    W, H = size
+    dem = synthetic_dem(21, 384)
+    cams = vf.orbit_cameras(5)
+    frames = {}
+    for full in (False, True):
+        if full:
+            monkeypatch.setenv("VF_RASTER_FULL", "1")
+        out = []
+        for mode, depth in (("northstar", False), ("northstar", True), ("shipped", False), ("shipped", True)):
+            sc = ext.Scene(W, H, grid=384, colormap="viridis")
+            sc.set_height_from_r32f(dem)
+            sc.set_shading(mode, depth=depth); sc.set_sun(40.0, 200.0); sc.set_exposure(1.2)
+            sc.set_auto_height_range()
+            out.append(sc.render_batch_rgba(cams))
+            vis = sc.debug_visibility()
+            assert (vis > 0).any() and (vis == 0).any()
+            out.append(vis)
+        frames[full] = out
+    for a, b in zip(frames[False], frames[True]):
+        assert np.array_equal(a, b)

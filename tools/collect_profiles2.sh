@@ -13,7 +13,7 @@ ncu -i $SRC/full_c5.ncu-rep --page raw --csv > $DST/${TAG}_ncu_full_c5_raw.csv
 ncu -i $SRC/raster_nocacheflush.ncu-rep --page raw --csv > $DST/${TAG}_ncu_k_raster_nocacheflush_raw.csv
 python tools/ncu_lines.py $SRC/full.ncu-rep k_geom_march 45 > $DST/${TAG}_k_geom_march_lines.txt
 python tools/ncu_regions.py $SRC/full.ncu-rep k_geom_march >> $DST/${TAG}_k_geom_march_lines.txt
-python tools/ncu_lines.py $SRC/full.ncu-rep k_raster 30 > $DST/${TAG}_k_raster_lines.txt
+python tools/ncu_lines.py $SRC/full.ncu-rep k_shade_list 30 > $DST/${TAG}_k_raster_lines.txt
 python tools/ncu_lines.py $SRC/full_c5.ncu-rep k_geom_march 30 > $DST/${TAG}_k_geom_march_c5_lines.txt
 python tools/ncu_regions.py $SRC/full_c5.ncu-rep k_geom_march >> $DST/${TAG}_k_geom_march_c5_lines.txt
 python tools/ncu_lines.py $SRC/full_c3d.ncu-rep k_geom_march 30 > $DST/${TAG}_k_geom_march_c3depth_lines.txt
@@ -25,7 +25,7 @@ out = {"source": f"profiles/{sys.argv[2]}_ncu_full_raw.csv (ncu --set full, dram
 def num(r, name, unit_row=rows[1]):
     i = h.index(name); v = float(r[i].replace(',', '')); u = unit_row[i]
     return v * {"Mbyte": 1e6, "Kbyte": 1e3, "Gbyte": 1e9, "byte": 1}.get(u, 1)
-for key, pat in (("k_geom", "k_geom_march"), ("k_raster", "k_raster")):
+for key, pat in (("k_geom", "k_geom_march"), ("k_raster", "k_shade_list"), ("k_resolve", "k_resolve_lean")):
     r = next(r for r in rows[2:] if pat in r[h.index("Kernel Name")])
     out[key] = int(num(r, "dram__bytes_read.sum") + num(r, "dram__bytes_write.sum"))
     out[key + "_warp_inst"] = int(num(r, "smsp__inst_executed.sum"))

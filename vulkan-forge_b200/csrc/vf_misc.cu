@@ -262,3 +262,44 @@ extern "C" int vf_selftest_div(uint64_t n_groups, uint32_t seed, uint64_t* misma
     *mismatches = (uint64_t)hres;
     return VF_OK;
 }
+
+// ---------------------------------------------------------------------------------------
+// vf_selftest_srgb: vf_srgb_encode_fast (guess + one correction) against vf_srgb_encode (binary search over the exact
+// thresholds) for every float from +0 to 1.0 inclusive, plus negative values, values above 1, infinities and NaNs.
+__global__ void __launch_bounds__(256)
+k_selftest_srgb(const float* __restrict__ thr_g, unsigned long long* __restrict__ bad) {
+    __shared__ float s_thr[257];
+    s_thr[threadIdx.x] = thr_g[threadIdx.x];
+    if (threadIdx.x == 0) s_thr[256] = __int_as_float(0x7f800000);
+    __syncthreads();
+    unsigned long long mine = 0ull;
+    const unsigned long long n_unit = 0x3f800000ull + 1ull, n_extra = 1ull << 24;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_unit + n_extra;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        // past the unit interval: bit patterns spread over (1, +inf], NaNs and the negative half
+        const uint32_t bits = i < n_unit ? (uint32_t)i : 0x3f800001u + (uint32_t)(i - n_unit) * 193u;
+        const float x = __uint_as_float(bits);
+        mine += vf_srgb_encode_fast(s_thr, x) != vf_srgb_encode(s_thr, x) ? 1ull : 0ull;
+    }
+    if (mine) atomicAdd(bad, mine);
+}
+
+extern "C" int vf_selftest_srgb(uint64_t* mismatches) {
+    if (!mismatches) return vf_set_error(VF_E_INVALID, "null output");
+    int rc = vf_require_device();
+    if (rc) return rc;
+    const float* thr = vf_srgb_thresholds_dev();
+    if (!thr) return VF_E_CUDA;
+    std::lock_guard<std::mutex> lk(vf_util_mutex());
+    cudaStream_t st = vf_util_stream();
+    unsigned long long* d = (unsigned long long*)vf_scratch(sizeof(unsigned long long));
+    if (!st || !d) return VF_E_CUDA;
+    VF_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long), st));
+    k_selftest_srgb<<<148 * 8, 256, 0, st>>>(thr, d);
+    VF_CUDA(cudaGetLastError());
+    unsigned long long hres = 0ull;
+    VF_CUDA(cudaMemcpyAsync(&hres, d, sizeof(hres), cudaMemcpyDeviceToHost, st));
+    VF_CUDA(cudaStreamSynchronize(st));
+    *mismatches = (uint64_t)hres;
+    return VF_OK;
+}

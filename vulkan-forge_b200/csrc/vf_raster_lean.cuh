@@ -81,22 +81,33 @@ k_resolve_lean(uint32_t W, uint32_t H, uint32_t w4_inv, uint32_t half, unsigned 
             if (out_vis) *reinterpret_cast<uint4*>(out_vis + p) = make_uint4(id[q][0], id[q][1], id[q][2], id[q][3]);
         }
     }
-    // compaction: exclusive scan of the threads' covered-pixel counts over the warp, one atomic per warp
+    // compaction: exclusive scan of the threads' covered-pixel counts over the warp, then over the CTA's eight warps, and
+    // ONE atomic per CTA (atomics on one address are served one after the other by its L2 slice: with one per warp the
+    // few thousand of a 1080p frame took longer than the streaming itself)
+    __shared__ uint32_t s_warp[8], s_base;
     uint32_t mine = 0u;
 #pragma unroll
     for (int q = 0; q < 2; ++q)
 #pragma unroll
         for (int b = 0; b < 4; ++b) mine += id[q][b] ? 1u : 0u;
-    if (__ballot_sync(0xffffffffu, mine != 0u) == 0u) return;
     uint32_t incl = mine;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const uint32_t v = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= (uint32_t)d) incl += v;
     }
-    uint32_t base = 0u;
-    if (lane == 31u) base = atomicAdd(&counters[VF_CNT_SHADE], incl);
-    base = __shfl_sync(0xffffffffu, base, 31);
+    const uint32_t wid = threadIdx.x >> 5;
+    if (lane == 31u) s_warp[wid] = incl;
+    __syncthreads();
+    if (threadIdx.x == 0u) {
+        uint32_t tot = 0u;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { const uint32_t c = s_warp[w]; s_warp[w] = tot; tot += c; }
+        s_base = tot ? atomicAdd(&counters[VF_CNT_SHADE], tot) : 0u;
+    }
+    __syncthreads();
+    if (mine == 0u) return;
+    const uint32_t base = s_base + s_warp[wid];
     uint32_t pos = base + incl - mine;
 #pragma unroll
     for (int q = 0; q < 2; ++q)

@@ -57,7 +57,7 @@ struct vf_scene {
     uint2* d_segtab = nullptr;           // k_geom_march row segments (first row, rows), rebuilt when G changes
     uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0, segtab_nfull = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
-    uint2* d_shade_list = nullptr;           // W*H entries: covered pixels of the frame (vf_raster_lean.cuh)
+    uint2* d_shade_list = nullptr;           // W*H entries: covered pixels of the frame (vf_raster_lean.cuh); nullptr: k_raster always
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
@@ -453,7 +453,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
         (void)cudaGetLastError();
         return vf_set_error(VF_E_OOM, "visibility buffer allocation failed");
     }
-    if ((w & 3) == 0 && cudaMalloc(&s->d_shade_list, (size_t)w * h * sizeof(uint2)) != cudaSuccess) {
+    if ((w & 3) == 0 && !getenv("VF_RASTER_FULL") && cudaMalloc(&s->d_shade_list, (size_t)w * h * sizeof(uint2)) != cudaSuccess) {
         scene_free(s);
         (void)cudaGetLastError();
         return vf_set_error(VF_E_OOM, "covered-pixel list allocation failed");
@@ -705,8 +705,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     // Frames that skip the binning stage take the two kernels without the merge / clipper paths (vf_raster_lean.cuh): a
     // streaming resolve that lists the covered pixels, then a dense shading pass over the list.  If the frame did queue
     // something, k_resolve_lean reports it like k_raster and the frame is rendered again.
-    static const bool raster_full = getenv("VF_RASTER_FULL") != nullptr;
-    if (skip_bins && !raster_full && s->d_shade_list != nullptr) {
+    if (skip_bins && s->d_shade_list != nullptr) {             // (VF_RASTER_FULL at scene creation: no list, k_raster in every frame)
         int& sms = g_dev_cache[s->device & 63].sm_count;
         if (!sms) VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
         const uint32_t w4 = s->W >> 2, quads = w4 * s->H, half = ((quads + 1u) / 2u + 255u) & ~255u;

@@ -125,9 +125,11 @@ k_shade_list(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     const uint32_t tid = threadIdx.x;
     s_thr[tid] = thr_g[tid];
     if (tid == 0u) s_thr[256] = __int_as_float(0x7f800000);
-    const uint32_t count = min(__ldcg(&counters[VF_CNT_SHADE]), f.W * f.H);
+    // The first entry is requested together with the length of the list, not after it (one L2 round trip less before the
+    // first shading instruction; an entry past the end is stale or unwritten memory of the list, read and dropped).
     uint32_t n = blockIdx.x * 256u + tid;
-    uint2 e = n < count ? __ldg(list + n) : make_uint2(0u, 0u);    // (requested before the barrier: part of the start-up wait)
+    uint2 e = __ldg(list + min(n, f.W * f.H - 1u));
+    const uint32_t count = min(__ldcg(&counters[VF_CNT_SHADE]), f.W * f.H);
     __syncthreads();
     for (; n < count; n += gridDim.x * 256u, e = n < count ? __ldg(list + n) : e) {
         const int px = (int)(e.x & 0xffffu), py = (int)(e.x >> 16);

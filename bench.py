@@ -279,11 +279,13 @@ def main():
 
     # ---- e2e_png: the same steps, frames delivered as .png files in pinned host memory (encoded on the device: only the
     # compressed bytes cross the bus) ----
+    # Pipelined like the raw leg: the DEM of step k+1 uploads (64 MiB H2D per step, inside the timed region) while step k
+    # renders, encodes and drains (render_batch_png_raw(..., next_height=) = vf_scene_render_batch_png_next).
     def png_run(steps):
         total = 0
-        for _ in range(steps):
-            sc.set_height_from_r32f_async(dem)
-            buf, sizes = sc.render_batch_png_raw(blocks)
+        sc.set_height_from_r32f_async(dem)
+        for k in range(steps):
+            buf, sizes = sc.render_batch_png_raw(blocks, next_height=dem if k + 1 < steps else None)
             total += int(sizes.sum()) + int(buf[0, 1])          # device->host result actually read
         return total
     png_steps = max(4, args.steps // 2)
@@ -351,7 +353,7 @@ def main():
                     "mpix_per_s": e2e_fps * W * H / 1e6},
             "e2e_png": {"value": png_fps, "unit": "frames/s", "steps": png_steps, "h2d_bytes_per_step": int(dem.nbytes + F * 176),
                         "d2h_bytes_per_step": int(png_bytes // png_steps),
-                        "note": "same steps, frames delivered as .png files in pinned host memory, encoded on the device (Scene.render_batch_png_raw)"},
+                        "note": "same steps, frames delivered as .png files in pinned host memory, encoded on the device; the DEM of step k+1 uploads while step k renders (Scene.render_batch_png_raw(cameras, next_height=...))"},
             "gpu_launches": args.steps * F * 3,   # k_geom_march + k_resolve_lean + k_shade_list per frame (value leg); k_binsort / k_raster only for frames that queue large or clipped triangles
             "parity": parity,
             "roofline": {"bound": "hbm", "limited_by": "instruction issue (see issue)", "kernel": {"ms_geom": "k_geom_march", "ms_bin": "k_binsort", "ms_raster": "k_resolve_lean + k_shade_list"}[dom],

@@ -190,6 +190,15 @@ int vf_scene_wait(vf_scene *s, int ticket);
  * 1.13 x the raw frame).  replaces: render + readback + image::save, src/scene/mod.rs:279-335, for batches. */
 size_t vf_png_file_bound(int w, int h);
 int vf_scene_render_batch_png(vf_scene *s, const float *u44xn, int n, uint8_t *out_host, size_t cap_per_file, uint32_t *sizes);
+/* The same with the NEXT batch's height image travelling meanwhile (DEM-tile jobs: SURVEY 8f-1 + 8f-2 together).  The batch
+ * is drawn from the current image (an upload pending at entry becomes current first, as in every render call); then, if
+ * next_height_host is not NULL, the upload of that image -- same size as the current one, pinned or pageable host memory that
+ * stays untouched until the next render call returns -- starts on the upload stream and overlaps this batch's rendering,
+ * encoding and read-back; it becomes current with the next render call.  flags: VF_PNG_KEEP_IMAGE = draw the current
+ * image again and leave a pending upload pending (for repeating a call that failed because a file did not fit its slot). */
+#define VF_PNG_KEEP_IMAGE 1
+int vf_scene_render_batch_png_next(vf_scene *scene, const float *u44xn, int n, uint8_t *out_host, size_t cap_per_file, uint32_t *sizes,
+                                   const float *next_height_host, uint32_t next_w, uint32_t next_h, int flags);
 /* n frames left in device memory (no D2H); for kernel-only timing */
 int vf_scene_render_device(vf_scene *s, const float *u44xn, int n);
 /* visibility of the last frame: per pixel 0 = clear colour, else primitive id + 1 */

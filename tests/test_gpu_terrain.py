@@ -619,3 +619,44 @@ def test_list_shading_equals_tile_kernel(ext, vf, synthetic_dem, monkeypatch, si
         frames[full] = out
     for a, b in zip(frames[False], frames[True]):
         assert np.array_equal(a, b)
+
+
+def test_png_batch_with_the_next_height_image_in_flight(ext, vf, synthetic_dem):
+    """render_batch_png_raw(cameras, next_height=...) (vf_scene_render_batch_png_next): the batch is drawn from the current
+    image while the NEXT call's image uploads; files equal those of the plain calls, image by image -- also when the first
+    attempt's host slots are too small and the call repeats itself (the staged upload must stay pending, not become current)."""
+    W, H, G = 320, 200, 256
+    dems = [synthetic_dem(31 + k, G) for k in range(3)]
+    cams = vf.orbit_cameras(4)
+    ref = ext.Scene(W, H, grid=G, colormap="terrain")
+    ref.set_shading("northstar", depth=True)
+    want = []
+    for d in dems:
+        ref.set_height_from_r32f(d); ref.set_height_range(-0.3, 0.3)
+        want.append(np.array(ref.render_batch_rgba(cams)))
+    sc = ext.Scene(W, H, grid=G, colormap="terrain")
+    sc.set_shading("northstar", depth=True); sc.set_height_range(-0.3, 0.3)
+    sc.set_height_from_r32f(dems[0])
+    for k in range(3):
+        buf, sizes = sc.render_batch_png_raw(cams, next_height=dems[k + 1] if k < 2 else None)
+        for f in range(len(cams)):
+            assert np.array_equal(_png_decode(bytes(buf[f, :sizes[f]]), W, H), want[k][f]), (k, f)
+    assert np.array_equal(sc.render_batch_rgba(cams), want[2])
+    with pytest.raises(Exception):
+        sc.render_batch_png_raw(cams, next_height=np.zeros((G, G + 4), np.float32))        # another size cannot be double-buffered
+    # incompressible frames: the first attempt does not fit its slots and is repeated with the staged upload pending
+    W, H, G = 512, 512, 1024
+    rng = np.random.default_rng(5)
+    noise = [rng.uniform(-0.05, 0.05, (G, G)).astype(np.float32) for _ in range(2)]
+    down = [((0.0, 3.0, 0.01), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 60.0, 0.1, 100.0)] * 2
+    ref = ext.Scene(W, H, grid=G, colormap="terrain"); ref.set_shading("northstar", depth=False); ref.set_height_range(-0.05, 0.05)
+    want = []
+    for d in noise:
+        ref.set_height_from_r32f(d); want.append(np.array(ref.render_batch_rgba(down)))
+    sc = ext.Scene(W, H, grid=G, colormap="terrain"); sc.set_shading("northstar", depth=False); sc.set_height_range(-0.05, 0.05)
+    sc.set_height_from_r32f(noise[0])
+    buf, sizes = sc.render_batch_png_raw(down, next_height=noise[1])
+    assert int(sizes[0]) > W * H * 4 // 4                                                 # larger than the first slot size: the call repeated itself
+    assert np.array_equal(_png_decode(bytes(buf[1, :sizes[1]]), W, H), want[0][1])
+    buf, sizes = sc.render_batch_png_raw(down)
+    assert np.array_equal(_png_decode(bytes(buf[0, :sizes[0]]), W, H), want[1][0])

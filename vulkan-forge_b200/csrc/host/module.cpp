@@ -215,11 +215,21 @@ public:
         if ((size_t)n != paths.size()) throw py::value_error("need one path per camera");
         png_batch(blocks.data(), n, &paths, nullptr);
     }
-    // n frames -> (pinned uint8 array (n, cap), uint32 sizes (n,)): file k is buf[k, :sizes[k]]; no copies on the host
-    py::tuple render_batch_png_raw(py::object cameras) {
+    // n frames -> (pinned uint8 array (n, cap), uint32 sizes (n,)): file k is buf[k, :sizes[k]]; no copies on the host.
+    // next_height: the float32[H,W] image (same size as the current one) the NEXT render call draws from; its upload overlaps
+    // this batch (vf_scene_render_batch_png_next) -- the pipelined form of set_height_from_r32f + render_batch_png_raw.
+    py::tuple render_batch_png_raw(py::object cameras, py::object next_height) {
         const std::vector<float> blocks = camera_blocks(cameras);
         const int n = (int)(blocks.size() / 44);
         if (n == 0) throw py::value_error("no cameras given");
+        py::array next;
+        if (!next_height.is_none()) {
+            if (!py::isinstance<py::array>(next_height)) throw py::type_error("argument 'next_height': expected a numpy float32 array");
+            next = py::reinterpret_borrow<py::array>(next_height);
+            if (next.ndim() != 2 || !next.dtype().is(py::dtype::of<float>()))
+                throw py::type_error("argument 'next_height': expected a 2-D numpy array of dtype float32");
+            if (!(next.flags() & py::array::c_style)) throw std::runtime_error("height must be C-contiguous float32[H,W]");
+        }
         py::array_t<uint32_t> sizes(n);
         uint32_t* sz = sizes.mutable_data();
         for (int attempt = 0; attempt < 2; ++attempt) {
@@ -229,10 +239,19 @@ public:
             bool ok;
             {
                 py::gil_scoped_release nogil;
-                ok = png_render(blocks.data(), n, p, cap, sz);
+                if (!next_height.is_none())              // the repeat draws the same image again; the upload is already on its way
+                    ok = png_render(blocks.data(), n, p, cap, sz, attempt == 0 ? static_cast<const float*>(next.data()) : nullptr,
+                                    (uint32_t)next.shape(1), (uint32_t)next.shape(0), attempt == 0 ? 0 : VF_PNG_KEEP_IMAGE);
+                else
+                    ok = png_render(blocks.data(), n, p, cap, sz);
             }
             encode_ms_ = 0.0f;
-            if (ok) return py::make_tuple(buf, sizes);
+            if (ok) {
+                // every upload issued before this (synchronous) call has been consumed; the one staged by it is in flight
+                pending_heights_.clear();
+                if (!next_height.is_none()) pending_heights_.push_back(next);
+                return py::make_tuple(buf, sizes);
+            }
         }
         throw std::runtime_error("PNG batch did not fit its worst-case slots");
     }
@@ -423,9 +442,11 @@ private:
         return std::min(bound, (want + 65535) & ~(size_t)65535);
     }
     // renders n frames into `p` (n x cap bytes); returns false if a file did not fit (then nothing is valid)
-    bool png_render(const float* blocks, int n, uint8_t* p, size_t cap, uint32_t* sizes) {
+    bool png_render(const float* blocks, int n, uint8_t* p, size_t cap, uint32_t* sizes, const float* next = nullptr, uint32_t next_w = 0,
+                    uint32_t next_h = 0, int flags = 0) {
         const size_t bound = (vf_png_file_bound((int)width_, (int)height_) + 255) & ~(size_t)255;
-        const int rc = vf_scene_render_batch_png(scene_, blocks, n, p, cap, sizes);
+        const int rc = (next || flags) ? vf_scene_render_batch_png_next(scene_, blocks, n, p, cap, sizes, next, next_w, next_h, flags)
+                                       : vf_scene_render_batch_png(scene_, blocks, n, p, cap, sizes);
         if (rc == VF_E_INVALID && cap < bound && std::string(vf_last_error()).rfind("PNG file", 0) == 0) { png_cap_hint_ = bound; return false; }
         check(rc);
         uint32_t mx = 0;

@@ -784,6 +784,9 @@ static int scene_apply_pending_dem(vf_scene* s) {
 // drains the other slot to the host.  Does not wait.
 static const int VF_PNG_SLOTS = 3;
 struct VfPngOut { uint8_t* out; size_t cap; uint32_t* sizes; };          // n files of at most `cap` bytes each, sizes[k] bytes used
+// the height image the call AFTER this one renders from: its upload starts as soon as this call's own image is current
+struct VfNextImage { const float* host; uint32_t w, h; };
+extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uint32_t w, uint32_t h);
 
 // file `j` of a PNG batch has been encoded into its slot: read its size, start the size-exact copy to the host
 static int png_collect(vf_scene* s, const VfPngOut& po, int j, vf_scene::Marks& mk) {
@@ -802,9 +805,17 @@ static int png_collect(vf_scene* s, const VfPngOut& po, int j, vf_scene::Marks& 
 }
 
 static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, int hslot,
-                        bool apply_pending, vf_scene::Marks& mk, const VfPngOut* png_out = nullptr) {
+                        bool apply_pending, vf_scene::Marks& mk, const VfPngOut* png_out = nullptr, const VfNextImage* next = nullptr) {
     int rc = apply_pending ? scene_apply_pending_dem(s) : VF_OK;
     if (rc) return rc;
+    if (next) {
+        // Only an image of the current size takes the double-buffered path; another size would replace the image
+        // this very batch is about to draw.
+        if (s->back_pending || next->w != s->Wd || next->h != s->Hd || !s->d_dem)
+            return vf_set_error(VF_E_INVALID, "the next height image must have the size of the current one (%u x %u), with no other upload pending", s->Wd, s->Hd);
+        rc = vf_scene_set_height_f32_async(s, next->host, next->w, next->h);
+        if (rc) return rc;
+    }
     rc = marks_init(mk);
     if (rc) return rc;
     if (png_out && !s->png) {
@@ -889,12 +900,13 @@ static int scene_check_overflow(vf_scene* s, int hslot, bool skipped_bins) {
 // for more queue / pair space than its buffer holds, the buffer is grown and the call is repeated
 // (an overflowed frame leaves a clean visibility buffer: k_raster always runs to completion).
 static int scene_render(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, uint32_t* d_vis, bool apply_pending = true,
-                        const VfPngOut* png_out = nullptr) {
+                        const VfPngOut* png_out = nullptr, const VfNextImage* next = nullptr) {
     if (!s || !u44xn || n <= 0) return vf_set_error(VF_E_INVALID, "invalid scene / frame count");
     int rc = scene_bind(s);
     if (rc) return rc;
     for (int attempt = 0; attempt < 8; ++attempt) {
-        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending, s->marks, png_out);
+        // (a repeated attempt draws the same image again: an upload staged by the first attempt stays pending)
+        rc = scene_submit(s, u44xn, n, out_host, d_vis, 0, apply_pending && attempt == 0, s->marks, png_out, attempt == 0 ? next : nullptr);
         if (rc) {                                            // nothing of the failed call may still be in flight when the caller reacts
             cudaStreamSynchronize(s->stream); cudaStreamSynchronize(s->copy_stream);
             return rc;
@@ -1052,6 +1064,15 @@ extern "C" int vf_scene_render_batch_png(vf_scene* s, const float* u44xn, int n,
     if (!s || !out_host || !sizes) return vf_set_error(VF_E_INVALID, "null argument");
     const VfPngOut po = {out_host, cap_per_file, sizes};
     return scene_render(s, u44xn ? u44xn : s->u44, n, nullptr, nullptr, true, &po);
+}
+
+extern "C" int vf_scene_render_batch_png_next(vf_scene* s, const float* u44xn, int n, uint8_t* out_host, size_t cap_per_file, uint32_t* sizes,
+                                             const float* next_height_host, uint32_t next_w, uint32_t next_h, int flags) {
+    if (!s || !out_host || !sizes) return vf_set_error(VF_E_INVALID, "null argument");
+    if (flags & ~VF_PNG_KEEP_IMAGE) return vf_set_error(VF_E_INVALID, "unknown flag");
+    const VfPngOut po = {out_host, cap_per_file, sizes};
+    const VfNextImage nx = {next_height_host, next_w, next_h};
+    return scene_render(s, u44xn ? u44xn : s->u44, n, nullptr, nullptr, !(flags & VF_PNG_KEEP_IMAGE), &po, next_height_host ? &nx : nullptr);
 }
 
 extern "C" int vf_scene_render_device(vf_scene* s, const float* u44xn, int n) {

@@ -103,14 +103,16 @@ int vf_png_dev_create(int w, int h, int slots, VfPngDev** out) {
     for (uint32_t j = 1; j < npow; ++j) pp[j] = host_gf_mul(pp[j - 1], xp);
     if ((err = cudaMalloc(&e->d_tables, tab.size() * 4)) != cudaSuccess) return fail("tables", err);
     if ((err = cudaMemcpy(e->d_tables, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess) return fail("tables", err);
-    if ((err = cudaMalloc(&e->d_file_size, (size_t)slots * 4)) != cudaSuccess) return fail("sizes", err);
+    if ((err = cudaHostAlloc(&e->h_file_size, (size_t)slots * 4, cudaHostAllocMapped)) != cudaSuccess) return fail("sizes", err);
+    if ((err = cudaHostGetDevicePointer(&e->d_file_size, e->h_file_size, 0)) != cudaSuccess) return fail("sizes", err);
+    for (int k = 0; k < slots; ++k) e->h_file_size[k] = 0u;
     *out = e;
     return VF_OK;
 }
 
 void vf_png_dev_destroy(VfPngDev* e) {
     if (!e) return;
-    cudaFree(e->d_bands); cudaFree(e->d_band_size); cudaFree(e->d_files); cudaFree(e->d_tables); cudaFree(e->d_file_size);
+    cudaFree(e->d_bands); cudaFree(e->d_band_size); cudaFree(e->d_files); cudaFree(e->d_tables); cudaFreeHost(e->h_file_size);
     (void)cudaGetLastError();
     delete e;
 }
@@ -151,8 +153,8 @@ extern "C" int vf_png_encode_rgba(const uint8_t* rgba_host, int w, int h, uint8_
     uint32_t fsz = 0;
     cudaError_t err = cudaMemcpyAsync(d_frame, rgba_host, fbytes, cudaMemcpyHostToDevice, st);
     if (err == cudaSuccess) { rc = vf_png_dev_encode(e, d_frame, 0, st); if (rc) { vf_png_dev_destroy(e); return rc; } }
-    if (err == cudaSuccess) err = cudaMemcpyAsync(&fsz, e->d_file_size, 4, cudaMemcpyDeviceToHost, st);
     if (err == cudaSuccess) err = cudaStreamSynchronize(st);
+    if (err == cudaSuccess) fsz = e->h_file_size[0];
     if (err == cudaSuccess && (fsz == 0xffffffffu || fsz > cap)) {
         vf_png_dev_destroy(e);
         return vf_set_error(VF_E_INVALID, "PNG file needs %u bytes, the output buffer holds %zu (size it with vf_png_file_bound)", fsz, cap);

@@ -13,7 +13,8 @@ struct VfPngDev {
     uint8_t* d_bands = nullptr;                            // nbands x band_cap
     uint32_t* d_band_size = nullptr; uint32_t* d_band_adler = nullptr;
     uint8_t* d_files = nullptr;                            // slots x file_cap: finished .png files
-    uint32_t* d_file_size = nullptr;                       // per slot (0xffffffff: did not fit, cannot happen with file_cap)
+    uint32_t* d_file_size = nullptr;                       // per slot (0xffffffff: did not fit, cannot happen with file_cap): the device's view of
+    uint32_t* h_file_size = nullptr;                       // ... mapped pinned host memory: k_png_pack stores the size where the host reads it (no copy on the stream)
     uint32_t* d_tables = nullptr;                          // IHDR preamble | x^(8r) | x^(8 * 64 j) mod the CRC polynomial
 };
 

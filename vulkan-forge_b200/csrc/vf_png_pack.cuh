@@ -115,5 +115,8 @@ k_png_pack(const uint8_t* __restrict__ bands, uint32_t out_cap, const uint32_t* 
         }
         if (first) for (uint32_t k = tid; k < 33u; k += VF_PNG_THREADS) file[k] = preamble[k];
     }
-    if (last && tid == 0u) *file_size = fits ? offset + total : 0xffffffffu;          // all ones: did not fit
+    if (last && tid == 0u) {                                                          // (file_size lies in mapped host memory)
+        *file_size = fits ? offset + total : 0xffffffffu;                             // all ones: did not fit
+        __threadfence_system();
+    }
 }

@@ -792,7 +792,7 @@ extern "C" int vf_scene_set_height_f32_async(vf_scene* s, const float* host, uin
 static int png_collect(vf_scene* s, const VfPngOut& po, int j, vf_scene::Marks& mk) {
     const int ps = j % VF_PNG_SLOTS;
     VF_CUDA(cudaEventSynchronize(s->ev_png_done[ps]));
-    const uint32_t size = s->h_png_size[ps];
+    const uint32_t size = s->png->h_file_size[ps];            // stored by k_png_pack straight into mapped host memory
     if (size == 0xffffffffu || size > po.cap)
         return vf_set_error(VF_E_INVALID, "PNG file %d needs %u bytes, the output slot holds %zu (size it with vf_png_file_bound)", j, size, po.cap);
     po.sizes[j] = size;
@@ -856,7 +856,6 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
             if (s->png_slot_used[ps]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_png_copied[ps], 0));
             rc = vf_png_dev_encode(s->png, s->d_frame + (size_t)slot * fbytes, ps, s->stream);
             if (rc) return rc;
-            VF_CUDA(cudaMemcpyAsync(&s->h_png_size[ps], s->png->d_file_size + ps, 4, cudaMemcpyDeviceToHost, s->stream));
             VF_CUDA(cudaEventRecord(s->ev_png_done[ps], s->stream));
             if (k >= VF_PNG_SLOTS - 1) { rc = png_collect(s, *png_out, k - (VF_PNG_SLOTS - 1), mk); if (rc) return rc; }
         }

@@ -32,7 +32,7 @@
 template <bool DEPTH>
 __global__ void __launch_bounds__(256)
 k_resolve_lean(uint32_t W, uint32_t H, uint32_t w4_inv, uint32_t half, unsigned long long* __restrict__ vis, uint32_t* __restrict__ counters,
-               uint32_t clear_rgba, uint8_t* __restrict__ out_rgba, uint32_t* __restrict__ out_vis, uint2* __restrict__ list,
+               uint32_t parity, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba, uint32_t* __restrict__ out_vis, uint2* __restrict__ list,
                uint32_t* __restrict__ high_water) {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t g0 = blockIdx.x * 256u + threadIdx.x, w4 = W >> 2, total = w4 * H;
@@ -103,7 +103,7 @@ k_resolve_lean(uint32_t W, uint32_t H, uint32_t w4_inv, uint32_t half, unsigned 
         uint32_t tot = 0u;
 #pragma unroll
         for (int w = 0; w < 8; ++w) { const uint32_t c = s_warp[w]; s_warp[w] = tot; tot += c; }
-        s_base = tot ? atomicAdd(&counters[VF_CNT_SHADE], tot) : 0u;
+        s_base = tot ? atomicAdd(&counters[VF_CNT_SHADE + parity], tot) : 0u;
     }
     __syncthreads();
     if (mine == 0u) return;
@@ -120,7 +120,7 @@ template <int MODE>
 __global__ void __launch_bounds__(256, VF_SHADE_CTAS)
 k_shade_list(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis, const float* __restrict__ dem,
              const float* __restrict__ hgrid, uint32_t hpitch, const float4* __restrict__ lut, const float* __restrict__ thr_g,
-             const uint32_t* __restrict__ counters, const uint2* __restrict__ list, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba) {
+             uint32_t* __restrict__ counters, uint32_t parity, const uint2* __restrict__ list, uint32_t clear_rgba, uint8_t* __restrict__ out_rgba) {
     __shared__ float s_thr[257];
     const uint32_t tid = threadIdx.x;
     s_thr[tid] = thr_g[tid];
@@ -129,7 +129,14 @@ k_shade_list(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     // first shading instruction; an entry past the end is stale or unwritten memory of the list, read and dropped).
     uint32_t n = blockIdx.x * 256u + tid;
     uint2 e = __ldg(list + min(n, f.W * f.H - 1u));
-    const uint32_t count = min(__ldcg(&counters[VF_CNT_SHADE]), f.W * f.H);
+    const uint32_t count = min(__ldcg(&counters[VF_CNT_SHADE + parity]), f.W * f.H);
+    // This is the frame's last kernel: it leaves the counter block as the next frame's first kernel wants it (the host
+    // then skips the memset between them).  The geometry pass's task and queue counters have no reader left; this
+    // frame's list length is still being read by other CTAs, so it is the OTHER parity's -- last read a frame ago, next
+    // written after this kernel -- that is reset here.
+    if ((blockIdx.x | tid) == 0u) {
+        counters[VF_CNT_TASK] = 0u; counters[VF_CNT_BIG] = 0u; counters[VF_CNT_SHADE + (parity ^ 1u)] = 0u;
+    }
     __syncthreads();
     for (; n < count; n += gridDim.x * 256u, e = n < count ? __ldg(list + n) : e) {
         const int px = (int)(e.x & 0xffffu), py = (int)(e.x >> 16);

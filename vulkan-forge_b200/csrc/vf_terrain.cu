@@ -58,6 +58,8 @@ struct vf_scene {
     uint32_t segtab_cap = 0, segtab_n = 0, segtab_G = 0, segtab_workers = 0, segtab_rows = 0, segtab_nfull = 0;
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     uint2* d_shade_list = nullptr;           // W*H entries: covered pixels of the frame (vf_raster_lean.cuh); nullptr: k_raster always
+    bool counters_clean = false;             // the last frame took the list-shading pass, whose kernels leave the counter block zeroed
+    uint32_t shade_parity = 0;               // which of the two list-length counters the next list-shading frame uses
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
     alignas(64) CUtensorMap dem_map;     // 2-D tiled map over the DEM (box 36x33 floats, k_geom)
@@ -657,7 +659,17 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     const float* thr = vf_srgb_thresholds_dev();
     if (!thr) return vf_set_error(VF_E_CUDA, "no sRGB table on device %d (vf_init has not run for it)", s->device);
     uint8_t* frame = s->d_frame + (size_t)slot * s->W * s->H * 4;
-    VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
+    // Counter block + tile counts start every frame at zero.  A frame that takes the list-shading pass leaves them that way
+    // itself (tile counts untouched, k_shade_list resets the task / queue counters and the OTHER frame parity's list
+    // length), so a run of such frames needs no memset node between k_shade_list(k) and k_geom_march(k+1).
+    static const bool bin_always = getenv("VF_BIN_ALWAYS") != nullptr;
+    const bool skip_bins = s->bin_hold == 0 && !bin_always;
+    const bool lean = skip_bins && s->d_shade_list != nullptr;
+    if (!(lean && s->counters_clean)) {
+        VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
+        s->shade_parity = 0;
+    }
+    s->counters_clean = false;                                 // (until this frame's kernels are all in the stream)
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[0], s->stream));
     if (s->visbuf_depth != f.depth) {     // (re)initialise the self-cleaning visibility buffer
         VF_CUDA(cudaMemsetAsync(s->d_visbuf, f.depth ? 0xff : 0x00, (size_t)s->W * s->H * 8, s->stream));
@@ -676,8 +688,6 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
-    static const bool bin_always = getenv("VF_BIN_ALWAYS") != nullptr;
-    const bool skip_bins = s->bin_hold == 0 && !bin_always;
     if (skip_bins) {
         s->submit_skipped_bins = true;
     } else {   // one cooperative launch: bin -> scan -> scatter with grid barriers in between
@@ -705,16 +715,17 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
     // Frames that skip the binning stage take the two kernels without the merge / clipper paths (vf_raster_lean.cuh): a
     // streaming resolve that lists the covered pixels, then a dense shading pass over the list.  If the frame did queue
     // something, k_resolve_lean reports it like k_raster and the frame is rendered again.
-    if (skip_bins && s->d_shade_list != nullptr) {             // (VF_RASTER_FULL at scene creation: no list, k_raster in every frame)
+    if (lean) {                                                // (VF_RASTER_FULL at scene creation: no list, k_raster in every frame)
         int& sms = g_dev_cache[s->device & 63].sm_count;
         if (!sms) VF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device));
         const uint32_t w4 = s->W >> 2, quads = w4 * s->H, half = ((quads + 1u) / 2u + 255u) & ~255u;
         const uint32_t w4_inv = (uint32_t)(0x100000000ull / w4 > 0xffffffffull ? 0xffffffffull : 0x100000000ull / w4);
-        if (f.depth) k_resolve_lean<true><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
-        else         k_resolve_lean<false><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
+        if (f.depth) k_resolve_lean<true><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, s->shade_parity, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
+        else         k_resolve_lean<false><<<half / 256u, 256, 0, s->stream>>>(s->W, s->H, w4_inv, half, s->d_visbuf, s->d_counters, s->shade_parity, clear, frame, d_vis, s->d_shade_list, s->d_maxpairs);
         const int ctas = sms * VF_SHADE_CTAS;
-        if (f.mode == VF_MODE_SHIPPED) k_shade_list<0><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->d_shade_list, clear, frame);
-        else                           k_shade_list<1><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->d_shade_list, clear, frame);
+        if (f.mode == VF_MODE_SHIPPED) k_shade_list<0><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->shade_parity, s->d_shade_list, clear, frame);
+        else                           k_shade_list<1><<<ctas, 256, 0, s->stream>>>(f, s->d_axis, s->d_dem, hg, hgp, s->d_lut, thr, s->d_counters, s->shade_parity, s->d_shade_list, clear, frame);
+        s->shade_parity ^= 1u;
     } else {
         if (f.mode == VF_MODE_SHIPPED) { if (f.depth) VF_RASTER_LAUNCH(0, true); else VF_RASTER_LAUNCH(0, false); }
         else                           { if (f.depth) VF_RASTER_LAUNCH(1, true); else VF_RASTER_LAUNCH(1, false); }
@@ -722,6 +733,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
 #undef VF_RASTER_LAUNCH
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[3], s->stream));
     VF_CUDA(cudaGetLastError());
+    s->counters_clean = lean;
     return VF_OK;
 }
 

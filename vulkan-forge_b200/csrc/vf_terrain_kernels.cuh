@@ -56,7 +56,7 @@ struct VfAxis { float coord; float uv; int tx; int ty; };   // 16 B per grid ind
 #define VF_SERIAL_AREA 4096    // shorter bbox axis and at most this many pixels of area; larger -> binned
 
 // counter block (cleared per frame together with the tile counts)
-enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_SHADE = 5, VF_CNT_WORDS = 8 };
+enum { VF_CNT_PAIRS = 0, VF_CNT_CLIPPED = 1, VF_CNT_BIG = 2, VF_CNT_TASK = 3, VF_CNT_GRIDBAR = 4, VF_CNT_SHADE = 5 /* and 6: one list length per frame parity */, VF_CNT_WORDS = 8 };
 
 // ---------------------------------------------------------------------------------------
 __global__ void k_axis(VfAxis* __restrict__ axis, uint32_t G, float step, float gm1,

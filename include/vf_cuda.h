@@ -201,6 +201,9 @@ int vf_scene_render_batch_png_next(vf_scene *scene, const float *u44xn, int n, u
                                    const float *next_height_host, uint32_t next_w, uint32_t next_h, int flags);
 /* n frames left in device memory (no D2H); for kernel-only timing */
 int vf_scene_render_device(vf_scene *s, const float *u44xn, int n);
+/* a frame left on the device by a render call: frame k of a batch is rendered into device slot k % 2, and stays there until
+ * another frame takes the slot.  Waits for the scene's streams; out_host: W * H * 4 bytes. */
+int vf_scene_read_frame(vf_scene *s, int slot, uint8_t *out_host);
 /* visibility of the last frame: per pixel 0 = clear colour, else primitive id + 1 */
 int vf_scene_debug_visibility(vf_scene *s, uint32_t *out_host);
 int vf_scene_enable_timing(vf_scene *s, int enabled);

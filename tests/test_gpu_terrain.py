@@ -660,3 +660,34 @@ def test_png_batch_with_the_next_height_image_in_flight(ext, vf, synthetic_dem):
     assert np.array_equal(_png_decode(bytes(buf[1, :sizes[1]]), W, H), want[0][1])
     buf, sizes = sc.render_batch_png_raw(down)
     assert np.array_equal(_png_decode(bytes(buf[0, :sizes[0]]), W, H), want[1][0])
+
+
+def test_geometry_pass_launched_behind_the_previous_frames_shading(ext, vf, synthetic_dem, monkeypatch):
+    """In a run of list-shading frames k_geom_march(k+1) is a programmatic dependent of k_shade_list(k) and starts on the
+    SMs that kernel's tail leaves idle (no memset node, no dependence between the two); VF_NO_PDL at scene creation keeps
+    the plain stream order.  Same frames either way: long device-resident batches (where the overlap happens), batches with
+    read-back, both modes, with and without depth, and a close-up in the middle that forces the binning stage back in."""
+    W, H, G = 640, 360, 512
+    dem = synthetic_dem(41, G)
+    cams = vf.orbit_cameras(24)
+    close = ((0.3, 0.4, 0.2), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 70.0, 0.05, 50.0)
+    mixed = cams[:7] + [close] + cams[7:14]
+    out = {}
+    for plain in (False, True):
+        if plain:
+            monkeypatch.setenv("VF_NO_PDL", "1")
+        res = []
+        for mode, depth in (("northstar", False), ("northstar", True), ("shipped", False)):
+            sc = ext.Scene(W, H, grid=G, colormap="magma")
+            sc.set_height_from_r32f(dem); sc.set_shading(mode, depth=depth); sc.set_auto_height_range()
+            sc.render_batch_device(cams)                     # frames stay on the device: nothing but kernels in the stream
+            sc.render_batch_device(cams)
+            last2 = [sc.read_device_frame((len(cams) - 2) % 2), sc.read_device_frame((len(cams) - 1) % 2)]
+            want2 = np.array(sc.render_batch_rgba(cams[-2:]))          # the same two cameras with read-back (events between frames)
+            assert np.array_equal(last2[0], want2[0]) and np.array_equal(last2[1], want2[1])
+            res += last2
+            res.append(np.array(sc.render_batch_rgba(mixed)))
+            res.append(sc.debug_visibility())
+        out[plain] = res
+    for a, b in zip(out[False], out[True]):
+        assert np.array_equal(a, b)

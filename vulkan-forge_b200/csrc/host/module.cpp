@@ -393,6 +393,12 @@ public:
         ticket_heights_.erase(ticket);                        // the batch is done, so are the uploads queued before it
         return out;
     }
+    // a frame left on the device by render_batch_device (frame k of a batch sits in slot k % 2)
+    py::array_t<uint8_t> read_device_frame(int slot) {
+        py::array_t<uint8_t> a({(py::ssize_t)height_, (py::ssize_t)width_, (py::ssize_t)4});
+        check(vf_scene_read_frame(scene_, slot, a.mutable_data()));
+        return a;
+    }
     // frames stay on the device; returns elapsed milliseconds (host clock around a synchronous call)
     double render_batch_device(py::object cameras) {
         const std::vector<float> blocks = camera_blocks(cameras);

@@ -136,8 +136,12 @@ k_shade_list(const __grid_constant__ VfFrame f, const VfAxis* __restrict__ axis,
     // written after this kernel -- that is reset here.
     if ((blockIdx.x | tid) == 0u) {
         counters[VF_CNT_TASK] = 0u; counters[VF_CNT_BIG] = 0u; counters[VF_CNT_SHADE + (parity ^ 1u)] = 0u;
+        __threadfence();
     }
     __syncthreads();
+    // the next frame's geometry pass, if it was launched as a programmatic dependent, may start wherever SMs fall idle
+    // (every CTA is past the counter reset above; nothing else of this kernel is read by it)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     for (; n < count; n += gridDim.x * 256u, e = n < count ? __ldg(list + n) : e) {
         const int px = (int)(e.x & 0xffffu), py = (int)(e.x >> 16);
         uint32_t rgba = clear_rgba;

@@ -59,6 +59,7 @@ struct vf_scene {
     unsigned long long* d_visbuf = nullptr;  // W*H visibility keys (L2-resident, self-cleaning)
     uint2* d_shade_list = nullptr;           // W*H entries: covered pixels of the frame (vf_raster_lean.cuh); nullptr: k_raster always
     bool counters_clean = false;             // the last frame took the list-shading pass, whose kernels leave the counter block zeroed
+    bool early_geom_ok = true;               // k_geom_march as a programmatic dependent of the previous frame's k_shade_list (VF_NO_PDL at creation: off)
     uint32_t shade_parity = 0;               // which of the two list-length counters the next list-shading frame uses
     int visbuf_depth = -1;               // which 'empty' value the buffer currently holds
     uint32_t* d_big = nullptr; uint32_t big_capacity = 0;   // queue of large / clipped primitives
@@ -455,6 +456,7 @@ extern "C" int vf_scene_create(int w, int h, uint32_t grid, int lut_id, int lut_
         (void)cudaGetLastError();
         return vf_set_error(VF_E_OOM, "visibility buffer allocation failed");
     }
+    s->early_geom_ok = getenv("VF_NO_PDL") == nullptr;
     if ((w & 3) == 0 && !getenv("VF_RASTER_FULL") && cudaMalloc(&s->d_shade_list, (size_t)w * h * sizeof(uint2)) != cudaSuccess) {
         scene_free(s);
         (void)cudaGetLastError();
@@ -567,7 +569,7 @@ static uint32_t clear_rgba8() {
 
 // k_geom_march: persistent grid of warp workers; rows per task shrink on coarse grids so that every
 // warp of the machine gets a few tasks
-static int launch_geom_march(vf_scene* s, const VfFrame& f) {
+static int launch_geom_march(vf_scene* s, const VfFrame& f, bool early) {
     VfDevCache& dc = g_dev_cache[s->device & 63];
     const size_t smem_d = VF_GM_WARPS * sizeof(VfGmWarpT<true>), smem_n = VF_GM_WARPS * sizeof(VfGmWarpT<false>);
     if (!dc.gm_attr) {                   // cudaFuncSetAttribute applies to the current device only
@@ -630,8 +632,17 @@ static int launch_geom_march(vf_scene* s, const VfFrame& f) {
         VF_CUDA(cudaMemsetAsync(d_dbg, 0, need * 8, s->stream));
     }
     static const bool no_safe = getenv("VF_GM_NO_SAFE") != nullptr;      // A/B: per-vertex clip tests in every task
-#define VF_GM_LAUNCH(T, D, S) k_geom_march<T, D, S><<<ctas, VF_GM_WARPS * 32, (D) ? smem_d : smem_n, s->stream>>>( \
-        f, s->dem_map_gm[(D) ? 1 : 0], s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters, s->d_segtab, nsegs, s->segtab_nfull, s->segtab_rows, (s->use_tma && !no_safe) ? s->d_hmm : nullptr, s->hmm_nb, dbg_path ? d_dbg : nullptr)
+    // early: programmatic dependent launch behind k_shade_list of the previous frame (see scene_enqueue)
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(VF_GM_WARPS * 32); cfg.stream = s->stream;
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization; pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = pdl; cfg.numAttrs = early ? 1u : 0u;
+    const float2* hmm_arg = (s->use_tma && !no_safe) ? s->d_hmm : nullptr;
+    unsigned long long* dbg_arg = dbg_path ? d_dbg : nullptr;
+#define VF_GM_LAUNCH(T, D, S) do { cfg.dynamicSmemBytes = (D) ? smem_d : smem_n; \
+        VF_CUDA(cudaLaunchKernelEx(&cfg, k_geom_march<T, D, S>, f, s->dem_map_gm[(D) ? 1 : 0], (const VfAxis*)s->d_axis, (const float*)s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, \
+                                   s->d_counters, (const uint2*)s->d_segtab, nsegs, s->segtab_nfull, s->segtab_rows, hmm_arg, s->hmm_nb, dbg_arg)); } while (0)
 #define VF_GM_LAUNCH2(T, D) do { if (f.mode == VF_MODE_SHIPPED) VF_GM_LAUNCH(T, D, true); else VF_GM_LAUNCH(T, D, false); } while (0)
     if (s->use_tma) { if (f.depth) VF_GM_LAUNCH2(true, true); else VF_GM_LAUNCH2(true, false); }
     else            { if (f.depth) VF_GM_LAUNCH2(false, true); else VF_GM_LAUNCH2(false, false); }
@@ -669,6 +680,11 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
         VF_CUDA(cudaMemsetAsync(s->d_tile_count, 0, ((size_t)s->n_tiles + VF_CNT_WORDS) * 4, s->stream));
         s->shade_parity = 0;
     }
+    // The kernel before this frame's k_geom_march in the stream is then k_shade_list of the previous frame, which the
+    // geometry pass does not depend on (it reads the list; the visibility buffer was reset by k_resolve_lean before it, the
+    // counters by its first CTA before it releases its dependents): k_geom_march may start on the SMs k_shade_list's tail
+    // leaves idle (programmatic dependent launch).  Not with per-kernel timing events in between.
+    const bool early_geom = s->early_geom_ok && lean && s->counters_clean && !s->timing;
     s->counters_clean = false;                                 // (until this frame's kernels are all in the stream)
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[0], s->stream));
     if (s->visbuf_depth != f.depth) {     // (re)initialise the self-cleaning visibility buffer
@@ -684,7 +700,7 @@ static int scene_enqueue(vf_scene* s, const float* u44, int slot, uint32_t* d_vi
             k_geom<false><<<dim3(gb, gb), VF_GEOM_THREADS, 0, s->stream>>>(
                 f, s->dem_map, s->d_axis, s->d_dem, s->d_visbuf, s->d_big, s->big_capacity, s->d_counters);
     } else {
-        int rc = launch_geom_march(s, f);
+        int rc = launch_geom_march(s, f, early_geom);
         if (rc) return rc;
     }
     if (s->timing) VF_CUDA(cudaEventRecord(s->ev[1], s->stream));
@@ -1088,6 +1104,17 @@ extern "C" int vf_scene_render_batch_png_next(vf_scene* s, const float* u44xn, i
 
 extern "C" int vf_scene_render_device(vf_scene* s, const float* u44xn, int n) {
     return scene_render(s, u44xn ? u44xn : (s ? s->u44 : nullptr), n, nullptr, nullptr);
+}
+
+extern "C" int vf_scene_read_frame(vf_scene* s, int slot, uint8_t* out_host) {
+    if (!s || !out_host) return vf_set_error(VF_E_INVALID, "null argument");
+    if (slot < 0 || slot >= VF_MAX_SLOTS) return vf_set_error(VF_E_INVALID, "frame slot must be 0 or 1");
+    if (int rc = scene_bind(s)) return rc;
+    const size_t fbytes = (size_t)s->W * s->H * 4;
+    VF_CUDA(cudaStreamSynchronize(s->stream));
+    VF_CUDA(cudaStreamSynchronize(s->copy_stream));
+    VF_CUDA(cudaMemcpy(out_host, s->d_frame + (size_t)slot * fbytes, fbytes, cudaMemcpyDeviceToHost));
+    return VF_OK;
 }
 
 extern "C" int vf_scene_debug_visibility(vf_scene* s, uint32_t* out_host) {

@@ -10,6 +10,9 @@ k_png_pack(const uint8_t* __restrict__ bands, uint32_t out_cap, const uint32_t* 
            const uint32_t* __restrict__ band_adler, const uint8_t* __restrict__ preamble /* 33 bytes */,
            const uint32_t* __restrict__ pow_piece, const uint32_t* __restrict__ pow_byte,
            uint8_t* __restrict__ file, uint32_t file_cap, uint32_t* __restrict__ file_size) {
+    // nothing that follows in a render stream reads this kernel's output on the device: the next frame's geometry pass,
+    // when launched as a programmatic dependent, may start beside it
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     extern __shared__ __align__(16) unsigned char png_smem[];
     __shared__ uint32_t s_tab[256];
     __shared__ uint32_t s_red[VF_PNG_THREADS];

@@ -867,6 +867,10 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
         if (s->slot_used[slot]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_copied[slot], 0));
         rc = scene_enqueue(s, u44xn + (size_t)k * 44, slot, d_vis);
         if (rc) return rc;
+        // (the previous frame's file is reported done only here, behind this frame's render kernels: nothing then stands
+        //  between k_png_pack(k-1) and k_geom_march(k) in the stream, and the geometry pass -- a programmatic dependent that
+        //  needs nothing from the encoder -- starts under it; the host collects files two frames late anyway)
+        if (png_out && k > 0) VF_CUDA(cudaEventRecord(s->ev_png_done[(k - 1) % VF_PNG_SLOTS], s->stream));
         if (out_host) {
             VF_CUDA(cudaEventRecord(s->ev_done[slot], s->stream));
             VF_CUDA(cudaStreamWaitEvent(s->copy_stream, s->ev_done[slot], 0));
@@ -884,7 +888,7 @@ static int scene_submit(vf_scene* s, const float* u44xn, int n, uint8_t* out_hos
             if (s->png_slot_used[ps]) VF_CUDA(cudaStreamWaitEvent(s->stream, s->ev_png_copied[ps], 0));
             rc = vf_png_dev_encode(s->png, s->d_frame + (size_t)slot * fbytes, ps, s->stream);
             if (rc) return rc;
-            VF_CUDA(cudaEventRecord(s->ev_png_done[ps], s->stream));
+            if (k == n - 1) VF_CUDA(cudaEventRecord(s->ev_png_done[ps], s->stream));
             if (k >= VF_PNG_SLOTS - 1) { rc = png_collect(s, *png_out, k - (VF_PNG_SLOTS - 1), mk); if (rc) return rc; }
         }
     }

@@ -8,16 +8,20 @@
 // leaves k_binsort out while frames queue nothing (vf_terrain.cu, "speculative binning") and renders a frame again with
 // the full pipeline when it turns out that one did; these kernels are what it launches in the first case.
 //
-// Why two kernels.  Shading one pixel is ~800 dependent instructions behind a key -> vertex heights -> normal taps chain of
+// Why two kernels.  Shading one pixel is ~600 dependent instructions behind a key -> vertex heights -> normal taps chain of
 // loads, several microseconds for a warp; an empty pixel is one load and one store.  A tile kernel (k_raster: CTA = tile,
 // thread = pixel) pays a CTA's launch and its load round trip for every tile of sky, keeps the empty lanes of a
 // half-covered warp waiting for the covered ones, and its duration is that of the warp with the most covered tiles
 // (ncu: at c3 only 14 % of the pixel warps shade anything, yet 1080p took 22 us however the loads were prefetched).
-//   k_resolve_lean : thread = 4 adjacent pixels, 16-byte accesses: takes the keys (and resets them for the next frame),
-//                    writes the clear colour, and appends every covered pixel as (x | y << 16, primitive) to a list --
-//                    one warp scan and one atomic per warp that has any.  Pure streaming.
+//   k_resolve_lean : thread = two quads of 4 adjacent pixels, 16-byte accesses: takes the keys (and resets them for the next
+//                    frame), writes the clear colour, and appends every covered pixel as (x | y << 16, primitive) to a
+//                    list -- warp scan, CTA scan, one atomic per CTA.  Pure streaming.
 //   k_shade_list   : persistent, thread = list entry: every lane of every warp shades (no empty lanes, equal work), no
-//                    calls, no stack, and the SM's warps all carry the long chain at once.
+//                    calls, no stack, and the SM's warps all carry the long chain at once.  It is the frame's last
+//                    kernel: it leaves the counter block zeroed for the next frame (the list length alternates between
+//                    two counters, one per frame parity), so that no memset node separates it from the next frame's
+//                    k_geom_march, which the host launches as its programmatic dependent: nothing passes from this
+//                    kernel to that one, and it starts on the SMs this kernel's tail leaves idle.
 // Results are those of k_raster, which the parity tests compare with the oracle through either path (VF_BIN_ALWAYS=1
 // keeps the binning stage and k_raster in every frame, VF_RASTER_FULL=1 keeps k_raster alone).
 #pragma once

@@ -691,3 +691,29 @@ def test_geometry_pass_launched_behind_the_previous_frames_shading(ext, vf, synt
         out[plain] = res
     for a, b in zip(out[False], out[True]):
         assert np.array_equal(a, b)
+
+
+def test_mode_and_depth_changes_between_memset_free_frames(ext, vf, synthetic_dem):
+    """One scene, runs of list-shading frames (no memset node, geometry pass launched under the previous shading tail) with
+    the depth test and the shading mode switched in between -- the visibility buffer is re-initialised, the key width
+    changes -- and two scenes taking turns on the same stream: every batch equals the one a fresh scene renders."""
+    W, H, G = 384, 216, 300
+    dem = synthetic_dem(51, G)
+    cams = vf.orbit_cameras(6)
+    def fresh(mode, depth):
+        sc = ext.Scene(W, H, grid=G, colormap="viridis")
+        sc.set_height_from_r32f(dem); sc.set_shading(mode, depth=depth); sc.set_height_range(-0.3, 0.4)
+        return np.array(sc.render_batch_rgba(cams))
+    want = {(m, d): fresh(m, d) for m in ("northstar", "shipped") for d in (False, True)}
+    a = ext.Scene(W, H, grid=G, colormap="viridis"); a.set_height_from_r32f(dem); a.set_height_range(-0.3, 0.4)
+    b = ext.Scene(W, H, grid=G, colormap="viridis"); b.set_height_from_r32f(dem); b.set_height_range(-0.3, 0.4)
+    seq = [("northstar", False), ("northstar", True), ("northstar", True), ("shipped", False), ("northstar", False), ("shipped", True)]
+    for k, (m, d) in enumerate(seq):
+        a.set_shading(m, depth=d)
+        a.render_batch_device(cams)
+        b.set_shading(*seq[-1 - k][:1], depth=seq[-1 - k][1])
+        b.render_batch_device(cams[:3])
+        got = [a.read_device_frame((len(cams) - 2) % 2), a.read_device_frame((len(cams) - 1) % 2)]
+        assert np.array_equal(got[0], want[(m, d)][-2]) and np.array_equal(got[1], want[(m, d)][-1]), (k, m, d)
+        assert np.array_equal(np.array(a.render_batch_rgba(cams)), want[(m, d)]), (k, m, d)
+        assert np.array_equal(b.read_device_frame(0), want[seq[-1 - k]][2]), k

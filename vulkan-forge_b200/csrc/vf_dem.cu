@@ -11,7 +11,10 @@
 #include <math.h>
 #include <string.h>
 
+#include <condition_variable>
+#include <functional>
 #include <thread>
+#include <vector>
 
 #include "vf_internal.h"
 
@@ -53,12 +56,26 @@ k_dem_select(const float* __restrict__ vals, uint32_t m, uint32_t rank0, uint32_
         if (tid < 512) hist[tid >> 8][tid & 255u] = 0u;
         __syncthreads();
         const uint32_t p0 = s_prefix[0], p1 = s_prefix[1];
-        for (uint32_t k = tid; k < m; k += 1024) {
-            const uint32_t key = vf_float_key(vals[k]);
+        // Heights of one terrain share their sign and exponent bits: in the first pass nearly every key falls into a handful
+        // of bins, and one shared-memory atomic per value would serialise on them.  The lanes of a warp that hit the same
+        // bin are found with match.any and their leader adds the count; while the two ranks still share their prefix (always
+        // in the first pass) one histogram serves both.
+        const bool same = p0 == p1;
+        const uint32_t lane = tid & 31u;
+        for (uint32_t k0 = 0; k0 < m; k0 += 1024) {          // (warp-uniform trip count: match.any needs the whole warp)
+            const uint32_t k = k0 + tid;
+            const uint32_t key = k < m ? vf_float_key(vals[k]) : 0u;
             const uint32_t bin = (key >> shift) & 255u;
-            if ((key & mask) == p0) atomicAdd(&hist[0][bin], 1u);
-            if ((key & mask) == p1) atomicAdd(&hist[1][bin], 1u);
+            const bool in0 = k < m && (key & mask) == p0, in1 = !same && k < m && (key & mask) == p1;
+            const uint32_t g0 = __match_any_sync(0xffffffffu, in0 ? bin : 256u);
+            if (in0 && lane == (uint32_t)__ffs((int)g0) - 1u) atomicAdd(&hist[0][bin], (uint32_t)__popc(g0));
+            if (!same) {
+                const uint32_t g1 = __match_any_sync(0xffffffffu, in1 ? bin : 256u);
+                if (in1 && lane == (uint32_t)__ffs((int)g1) - 1u) atomicAdd(&hist[1][bin], (uint32_t)__popc(g1));
+            }
         }
+        __syncthreads();
+        if (same && tid < 256) hist[1][tid] = hist[0][tid];
         __syncthreads();
         if (tid < 2) {
             uint32_t r = s_rank[tid], cum = 0u, b = 0u;
@@ -268,6 +285,59 @@ int vf_dem_minmax_device(const float* d_data, uint32_t w, uint32_t h, uint32_t p
 static const size_t kChunkFloats = 16u << 20;
 static int vf_dem_stats_locked(const float* data, size_t n, float out4[4], cudaStream_t st);
 
+// Helper threads for the strided host gather of vf_dem_minmax(clamp = 1): parked on a condition variable between calls
+// (creating threads per call cost more than the gather they shared), started on first use, joined at unload.
+namespace {
+class VfGatherPool {
+public:
+    explicit VfGatherPool(int helpers) {
+        for (int t = 0; t < helpers; ++t) th_.emplace_back([this, t] { loop(t); });
+    }
+    ~VfGatherPool() {
+        { std::lock_guard<std::mutex> lk(mu_); stop_ = true; ++gen_; }
+        go_.notify_all();
+        for (auto& t : th_) t.join();
+    }
+    int parts() const { return (int)th_.size() + 1; }
+    // f(part) for part = 0 .. parts() - 1, the last one on the calling thread; returns when all are done
+    void run(const std::function<void(int)>& f) {
+        { std::lock_guard<std::mutex> lk(mu_); job_ = &f; pending_ = (int)th_.size(); ++gen_; }
+        go_.notify_all();
+        f((int)th_.size());
+        std::unique_lock<std::mutex> lk(mu_);
+        done_.wait(lk, [this] { return pending_ == 0; });
+        job_ = nullptr;
+    }
+private:
+    void loop(int t) {
+        uint64_t seen = 0;
+        for (;;) {
+            const std::function<void(int)>* f;
+            {
+                std::unique_lock<std::mutex> lk(mu_);
+                go_.wait(lk, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (stop_) return;
+                f = job_;
+            }
+            (*f)(t);
+            { std::lock_guard<std::mutex> lk(mu_); if (--pending_ == 0) done_.notify_one(); }
+        }
+    }
+    std::vector<std::thread> th_;
+    std::mutex mu_;
+    std::condition_variable go_, done_;
+    const std::function<void(int)>* job_ = nullptr;
+    uint64_t gen_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+};
+VfGatherPool& vf_gather_pool() {
+    static VfGatherPool pool((int)std::min(7u, std::max(1u, std::thread::hardware_concurrency()) - 1u));
+    return pool;
+}
+}   // namespace
+
 extern "C" int vf_dem_minmax(const float* data, size_t n, int clamp, float* lo, float* hi) {
     if (!data || !lo || !hi) return vf_set_error(VF_E_INVALID, "null argument");
     if (n == 0) return vf_set_error(VF_E_INVALID, "heightmap slice empty");
@@ -286,7 +356,7 @@ extern "C" int vf_dem_minmax(const float* data, size_t n, int clamp, float* lo, 
         char* sc = (char*)vf_scratch(256 + m * 4);
         if (!stage || !sc) return VF_E_OOM;
         // (every sample is a cache and, at large strides, a TLB miss: software prefetch keeps ~32 of them in flight per
-        // thread, four threads share the work on large arrays)
+        // thread, up to eight parked threads share the work on large arrays)
         auto gather = [&](size_t k0, size_t k1) {
             for (size_t k = k0; k < k1; ++k) {
                 if (k + 32 < k1) __builtin_prefetch(data + (k + 32) * step, 0, 0);
@@ -294,10 +364,9 @@ extern "C" int vf_dem_minmax(const float* data, size_t n, int clamp, float* lo, 
             }
         };
         if (step >= 64 && m >= 16384) {
-            std::thread th[3];
-            for (int t = 0; t < 3; ++t) th[t] = std::thread(gather, m * (t + 1) / 4, m * (t + 2) / 4);
-            gather(0, m / 4);
-            for (auto& t : th) t.join();
+            VfGatherPool& pool = vf_gather_pool();
+            const size_t parts = (size_t)pool.parts();
+            pool.run([&](int part) { gather(m * (size_t)part / parts, m * ((size_t)part + 1) / parts); });
         } else {
             gather(0, m);
         }

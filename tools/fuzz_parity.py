@@ -155,6 +155,23 @@ def random_dem_values(rng):
         return np.ascontiguousarray(a, np.float32), kind
 
 
+def png_decode(data, w, h):
+    """chunk walk + zlib (checks the Adler-32) + Sub / None filters -> (h, w, 4) uint8"""
+    import struct, zlib
+    pos, idat = 8, []
+    while pos < len(data):
+        ln, typ = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + ln]
+        assert zlib.crc32(typ + body) == struct.unpack(">I", data[pos + 8 + ln:pos + 12 + ln])[0]
+        if typ == b"IDAT": idat.append(body)
+        pos += 12 + ln
+    raw = np.frombuffer(zlib.decompress(b"".join(idat)), np.uint8).reshape(h, 4 * w + 1)
+    px = raw[:, 1:].reshape(h, w, 4).astype(np.uint32)
+    sub = raw[:, 0] == 1
+    px[sub] = np.cumsum(px[sub], axis=1) & 255
+    return px.astype(np.uint8)
+
+
 def fuzz_dem(budget, seed):
     """dem_minmax (min/max and the 1-99 % percentile pair of src/terrain_stats.rs:11-35) bit-for-bit."""
     ext = vf._vulkan_forge
@@ -242,6 +259,19 @@ def fuzz_api(budget, seed):
             got = sc.render_batch_rgba(cams)
             if not np.array_equal(got, want[1]):
                 ok = False; desc["failed"].append(("sync-batch", [int((got[i] != want[1][i]).any(-1).sum()) for i in range(len(cams))]))
+            # PNG batches with the next image in flight (same-size images only), then frames left on the device
+            # (runs of frames without a memset node, the geometry pass launched under the previous shading tail)
+            if W <= 8192:
+                for k in range(3):
+                    buf, sizes = sc.render_batch_png_raw(cams, next_height=dems[k & 1] if k < 2 else None)
+                    which = (k + 1) & 1                     # image drawn by call k: dems[1], dems[0], dems[1]
+                    for i in range(len(cams)):
+                        if not np.array_equal(png_decode(bytes(buf[i, :sizes[i]]), W, H), want[which][i]):
+                            ok = False; desc["failed"].append(("png-next", k, i)); break
+            sc.render_batch_device(cams * 3)
+            last = sc.read_device_frame((3 * len(cams) - 1) % 2)
+            if not np.array_equal(last, want[1][-1]):
+                ok = False; desc["failed"].append(("device-batch", int((last != want[1][-1]).any(-1).sum())))
             if not ok:                                      # is the reference scene itself stable?
                 ref_sc.set_height_from_r32f(dems[1])
                 again = []

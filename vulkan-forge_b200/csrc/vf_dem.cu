@@ -333,7 +333,12 @@ private:
     bool stop_ = false;
 };
 VfGatherPool& vf_gather_pool() {
-    static VfGatherPool pool((int)std::min(7u, std::max(1u, std::thread::hardware_concurrency()) - 1u));
+    static VfGatherPool pool([] {
+        const char* e = getenv("VF_GATHER_THREADS");              // tuning aid: total threads of the gather, caller included
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const unsigned want = e ? (unsigned)std::max(1, atoi(e)) : 8u;
+        return (int)(std::min(want, hw) - 1u);
+    }());
     return pool;
 }
 }   // namespace
